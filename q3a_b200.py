@@ -1,0 +1,12 @@
+"""Import alias: the package directory is `qwen3-asr.cpp_b200/` (not a legal Python identifier),
+so `import q3a_b200` loads it under this name."""
+import importlib.util
+import os
+import sys
+
+_pkg_dir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "qwen3-asr.cpp_b200")
+_spec = importlib.util.spec_from_file_location(
+    "q3a_b200", os.path.join(_pkg_dir, "__init__.py"), submodule_search_locations=[_pkg_dir])
+_mod = importlib.util.module_from_spec(_spec)
+sys.modules["q3a_b200"] = _mod
+_spec.loader.exec_module(_mod)
