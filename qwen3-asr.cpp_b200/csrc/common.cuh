@@ -6,6 +6,9 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <vector>
+
+#include "../../include/q3a.h"
 
 namespace q3a {
 
@@ -23,17 +26,14 @@ const char* last_error();
         }                                                                                    \
     } while (0)
 
-enum : int {
-    Q3A_OK = 0,
-    Q3A_ERR_ARG = 1,
-    Q3A_ERR_CUDA = 2,
-    Q3A_ERR_IO = 3,
-    Q3A_ERR_FORMAT = 4,
-    Q3A_ERR_STATE = 5,
-};
+#define Q3A_TRY(expr)                     \
+    do {                                  \
+        int _rc = (expr);                 \
+        if (_rc != Q3A_OK) return _rc;    \
+    } while (0)
 
 // operand element type fed to the tensor cores (accumulation is always fp32)
-enum : int { OP_BF16 = 0, OP_F16 = 1 };
+enum : int { OP_BF16 = Q3A_OP_BF16, OP_F16 = Q3A_OP_F16 };
 
 template <typename T> struct OpTraits;
 template <> struct OpTraits<__nv_bfloat16> {
@@ -63,7 +63,7 @@ template <> struct OpTraits<__half> {
     }
 };
 
-// ggml_gelu is the tanh form (audio_encoder.cpp:112 → ggml_gelu); MUFU.TANH is accurate to
+// ggml_gelu is the tanh form (audio_encoder.cpp:112 -> ggml_gelu); MUFU.TANH is accurate to
 // ~2^-11 relative, the same order as the f16 table ggml's CPU path reads it through.
 __device__ __forceinline__ float gelu_tanh(float x) {
     const float k0 = 0.7978845608028654f, k1 = 0.044715f;
@@ -74,5 +74,70 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 }
 
 __host__ __device__ constexpr int ceil_div(int a, int b) { return (a + b - 1) / b; }
+__host__ __device__ constexpr int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+__host__ __device__ constexpr int64_t round_up64(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// ---- small RAII helpers (host) ---------------------------------------------------------------
+// Growable device buffer: keeps its allocation between calls, grows geometrically.
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return Q3A_OK;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 8 + 256;
+        Q3A_CUDA(cudaMalloc(&p, want));
+        cap = want;
+        return Q3A_OK;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+// Ring of pinned host staging slots for per-call descriptor tables: a slot is reused only after the
+// async copy that read it has completed (event), so back-to-back async calls never race.
+struct PinnedRing {
+    static constexpr int kSlots = 4;
+    void* host[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+    size_t cap[kSlots] = {0, 0, 0, 0};
+    cudaEvent_t ev[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+    bool pending[kSlots] = {false, false, false, false};
+    int next = 0;
+    // returns a host pointer of at least `bytes`; call mark(stream) after enqueueing the copy
+    int acquire(size_t bytes, void** out) {
+        int s = next;
+        if (pending[s]) { Q3A_CUDA(cudaEventSynchronize(ev[s])); pending[s] = false; }
+        if (bytes > cap[s]) {
+            if (host[s]) cudaFreeHost(host[s]);
+            host[s] = nullptr; cap[s] = 0;
+            Q3A_CUDA(cudaMallocHost(&host[s], bytes + 4096));
+            cap[s] = bytes + 4096;
+        }
+        if (!ev[s]) Q3A_CUDA(cudaEventCreateWithFlags(&ev[s], cudaEventDisableTiming));
+        *out = host[s];
+        return Q3A_OK;
+    }
+    int mark(cudaStream_t st) {
+        int s = next;
+        Q3A_CUDA(cudaEventRecord(ev[s], st));
+        pending[s] = true;
+        next = (next + 1) % kSlots;
+        return Q3A_OK;
+    }
+    void release() {
+        for (int s = 0; s < kSlots; ++s) {
+            if (pending[s]) cudaEventSynchronize(ev[s]);
+            if (host[s]) cudaFreeHost(host[s]);
+            if (ev[s]) cudaEventDestroy(ev[s]);
+            host[s] = nullptr; ev[s] = nullptr; cap[s] = 0; pending[s] = false;
+        }
+    }
+};
+
+// make `device` current and check that it is an sm_100 part (there is no other code path)
+int use_device(int device);
+
+// counts our kernel launches (reported through q3a_timings::total_launches)
+extern thread_local int g_launch_counter;
 
 }  // namespace q3a

@@ -24,7 +24,7 @@ __device__ __forceinline__ void store8_f32(float* p, const float (&v)[8]) {
     *(reinterpret_cast<float4*>(p) + 1) = make_float4(v[4], v[5], v[6], v[7]);
 }
 
-// out[m][n] = act(acc + bias[n])  → 16-bit operand for the next GEMM
+// out[m][n] = act(acc + bias[n])  -> 16-bit operand for the next GEMM
 template <class OpT, bool kGelu>
 struct EpiBiasActOp {
     OpT* out; int ldc; const float* bias;
@@ -46,7 +46,7 @@ struct EpiBiasActOp {
     }
 };
 
-// out[m][n] = acc + bias[n] (+ res[m][n])  → fp32 (residual stream / final features); res may alias out
+// out[m][n] = acc + bias[n] (+ res[m][n])  -> fp32 (residual stream / final features); res may alias out
 template <bool kResidual>
 struct EpiBiasF32 {
     float* out; int ldc; const float* bias; const float* res;
@@ -73,20 +73,84 @@ struct EpiBiasF32 {
 };
 
 // conv_out: x[m][n] = acc + pe[pos[m]][n]   (sinusoidal table restarts per stem chunk,
-// audio_encoder.cpp:400-404 / forced_aligner.cpp:718-735)
+// audio_encoder.cpp:400-404 / forced_aligner.cpp:718-735); pe == nullptr -> plain store (conv-only mode)
 struct EpiPosEmbF32 {
     float* out; int ldc; const float* pe; const int* pos;
     __device__ __forceinline__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const {
         float* row = out + (size_t)m * ldc + n0;
-        const float* prow = pe + (size_t)__ldg(pos + m) * ldc + n0;
+        const float* prow = pe ? pe + (size_t)__ldg(pos + m) * ldc + n0 : nullptr;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
                 float p[8], v[8];
-                load8(prow + g * 8, p);
+                if (pe) load8(prow + g * 8, p);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j] + p[j];
+                for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j] + (pe ? p[j] : 0.0f);
                 store8_f32(row + g * 8, v);
+            }
+        }
+    }
+};
+
+// ---- stem epilogues (layout: stem.cuh) -------------------------------------------------------
+// conv2: GELU(acc + bias) -> the parity-split planes conv3 reads.  GEMM row m = R_out*OF + of with
+// R_out = chunk*P + 1 + ot (row chunk*P is the zero pad row of the implicit GEMM and is skipped).
+// Positions past the chunk's valid length are written as zeros so that a shorter tail chunk sees the
+// convolution's zero padding instead of stale data.
+template <class OpT>
+struct EpiConvToPlanes {
+    OpT* planes;            // next conv's input: [4][R_cap_next][OF/2][C]
+    const float* bias;
+    const int* ot_valid;    // per chunk: valid output time steps of this conv
+    int C, OF, P, P_next;
+    long long plane_stride; // R_cap_next * (OF/2) * C elements
+    __device__ __forceinline__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const {
+        const int r_out = m / OF, of = m - r_out * OF;
+        const int chunk = r_out / P, j = r_out - chunk * P;
+        if (j == 0) return;
+        const int ot = j - 1;
+        const bool valid = ot < __ldg(ot_valid + chunk);
+        const int plane = ((ot & 1) << 1) | (of & 1);
+        const long long row = (long long)chunk * P_next + 1 + (ot >> 1);
+        OpT* dst = planes + plane * plane_stride + (row * (OF >> 1) + (of >> 1)) * C + n0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float b[8], v[8];
+                load8(bias + n0 + g * 8, b);
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj) v[jj] = valid ? gelu_tanh(acc[g * 8 + jj] + b[jj]) : 0.0f;
+                store8_op<OpT>(dst + g * 8, v);
+            }
+        }
+    }
+};
+
+// conv3: GELU(acc + bias) -> token-major feature rows for conv_out.  Feature order inside a row is
+// of*C + channel (the conv_out weight columns are permuted to match at load time; the reference's
+// order is channel*16 + of, audio_encoder.cpp:139-142).  Only the tokens the mode keeps are written.
+template <class OpT>
+struct EpiConvToFeat {
+    OpT* feat;              // [tokens][OF*C]
+    const float* bias;
+    const int* n_tok;       // per chunk: tokens kept
+    const int* tok_base;    // per chunk: first token row
+    int C, OF, P;
+    __device__ __forceinline__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const {
+        const int r_out = m / OF, of = m - r_out * OF;
+        const int chunk = r_out / P, j = r_out - chunk * P;
+        if (j == 0) return;
+        const int ot = j - 1;
+        if (ot >= __ldg(n_tok + chunk)) return;
+        OpT* dst = feat + ((long long)(__ldg(tok_base + chunk) + ot) * OF + of) * C + n0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float b[8], v[8];
+                load8(bias + n0 + g * 8, b);
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj) v[jj] = gelu_tanh(acc[g * 8 + jj] + b[jj]);
+                store8_op<OpT>(dst + g * 8, v);
             }
         }
     }

@@ -1,0 +1,49 @@
+// Host launchers for the tcgen05 GEMM (gemm_tc.cuh) with the fused epilogues of epilogues.cuh.
+#pragma once
+#include "common.cuh"
+
+namespace q3a {
+
+enum EpiKind : int {
+    EPI_BIAS_OP = 0,        // 16-bit out = acc + bias
+    EPI_BIAS_GELU_OP = 1,   // 16-bit out = gelu(acc + bias)
+    EPI_BIAS_F32 = 2,       // f32 out = acc + bias
+    EPI_BIAS_RES_F32 = 3,   // f32 out = acc + bias + res
+    EPI_POSEMB_F32 = 4,     // f32 out = acc + pe[pos[m]]
+};
+
+struct LinearArgs {
+    const void* a = nullptr;   // [M][K] 16-bit, leading dimension lda
+    int M = 0, K = 0, lda = 0;
+    const void* w = nullptr;   // [N][K] 16-bit, leading dimension ldw
+    int N = 0, ldw = 0;
+    void* out = nullptr;       // [M][ldc], 16-bit or f32 depending on the epilogue
+    int ldc = 0;
+    const float* bias = nullptr;
+    const float* res = nullptr;
+    const float* pe = nullptr;
+    const int* pos = nullptr;
+    int block_n = 0;           // 0 = pick from N
+};
+
+int gemm_linear(EpiKind kind, int fmt, const LinearArgs& a, cudaStream_t stream);
+
+struct ConvArgs {
+    const void* planes = nullptr;  // input [4][R_cap][Fh][C] 16-bit
+    int R_cap = 0, R_used = 0, Fh = 0, C = 0;
+    const void* w = nullptr;       // [N][9 * cpad] 16-bit, cpad = ceil(C/64)*64, k = tap*cpad + c
+    int N = 0;
+    const float* bias = nullptr;
+    int P = 0;                     // rows per chunk of this conv's row space
+    // to-planes epilogue (conv2)
+    void* out_planes = nullptr; int P_next = 0; long long out_plane_stride = 0; const int* ot_valid = nullptr;
+    // to-features epilogue (conv3)
+    void* feat = nullptr; const int* n_tok = nullptr; const int* tok_base = nullptr;
+};
+
+int gemm_conv(bool to_feat, int fmt, const ConvArgs& a, cudaStream_t stream);
+
+int pick_block_n(int N);
+int sm_count();
+
+}  // namespace q3a

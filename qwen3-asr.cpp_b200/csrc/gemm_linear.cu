@@ -1,0 +1,102 @@
+// Linear layers on the tcgen05 GEMM: instantiations and host dispatch.
+#include "gemm.h"
+#include "gemm_tc.cuh"
+#include "epilogues.cuh"
+#include "tmap.h"
+
+namespace q3a {
+
+int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    }
+    return n;
+}
+
+int pick_block_n(int N) {
+    if (N % 256 == 0) return 256;
+    if (N % 224 == 0) return 224;
+    if (N % 240 == 0) return 240;
+    if (N >= 1024) return 256;
+    return 128;
+}
+
+template <int BLOCK_N, int kFmt, class Epi>
+static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t stream) {
+    using S = GemmSmem<BLOCK_N>;
+    CUtensorMap ta, tb;
+    Q3A_TRY(make_tmap_2d(&ta, a.a, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, kBlockM));
+    Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldw, BLOCK_N));
+    auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderLinear, Epi>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        Q3A_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+        attr_set = true;
+    }
+    LoaderLinear loader{ceil_div(a.K, kBlockK)};
+    const int tiles = ceil_div(a.M, kBlockM) * ceil_div(a.N, BLOCK_N);
+    const int grid = tiles < sm_count() ? tiles : sm_count();
+    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, a.M, a.N, loader, epi);
+    ++g_launch_counter;
+    Q3A_CUDA(cudaGetLastError());
+    return Q3A_OK;
+}
+
+template <int BLOCK_N, int kFmt>
+static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) {
+    using OpT = typename std::conditional<kFmt == 1, __nv_bfloat16, __half>::type;
+    switch (kind) {
+        case EPI_BIAS_OP:
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, false>{(OpT*)a.out, a.ldc, a.bias}, stream);
+        case EPI_BIAS_GELU_OP:
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, true>{(OpT*)a.out, a.ldc, a.bias}, stream);
+        case EPI_BIAS_F32:
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<false>{(float*)a.out, a.ldc, a.bias, nullptr}, stream);
+        case EPI_BIAS_RES_F32:
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<true>{(float*)a.out, a.ldc, a.bias, a.res}, stream);
+        case EPI_POSEMB_F32:
+            return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32{(float*)a.out, a.ldc, a.pe, a.pos}, stream);
+    }
+    set_error("gemm_linear: unknown epilogue");
+    return Q3A_ERR_ARG;
+}
+
+template <int kFmt>
+static int dispatch_bn(EpiKind kind, const LinearArgs& a, int bn, cudaStream_t stream) {
+    switch (bn) {
+        case 128: return dispatch_epi<128, kFmt>(kind, a, stream);
+        case 224: return dispatch_epi<224, kFmt>(kind, a, stream);
+        case 256: return dispatch_epi<256, kFmt>(kind, a, stream);
+    }
+    set_error("gemm_linear: unsupported block_n " + std::to_string(bn));
+    return Q3A_ERR_ARG;
+}
+
+int gemm_linear(EpiKind kind, int fmt, const LinearArgs& a, cudaStream_t stream) {
+    if (a.M <= 0) return Q3A_OK;
+    if (a.K % 8 || a.N % 8 || a.lda % 8 || a.ldw % 8 || a.K <= 0 || a.N <= 0) {
+        set_error("gemm_linear: K, N and leading dimensions must be positive multiples of 8");
+        return Q3A_ERR_ARG;
+    }
+    int bn = a.block_n ? a.block_n : pick_block_n(a.N);
+    if (bn == 240) bn = 128;
+    return fmt == OP_F16 ? dispatch_bn<0>(kind, a, bn, stream) : dispatch_bn<1>(kind, a, bn, stream);
+}
+
+}  // namespace q3a
+
+extern "C" int q3a_test_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, float* d_dev, int M, int N,
+                             int K, int operand_dtype, int block_n, void* stream) {
+    using namespace q3a;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device"); return Q3A_ERR_CUDA; }
+    Q3A_TRY(use_device(dev));
+    LinearArgs a;
+    a.a = a_dev; a.M = M; a.K = K; a.lda = K;
+    a.w = w_dev; a.N = N; a.ldw = K;
+    a.out = d_dev; a.ldc = N; a.bias = bias_dev; a.block_n = block_n;
+    return gemm_linear(EPI_BIAS_F32, operand_dtype, a, reinterpret_cast<cudaStream_t>(stream));
+}

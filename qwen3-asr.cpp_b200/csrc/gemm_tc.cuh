@@ -1,15 +1,15 @@
-// Persistent warp-specialised tcgen05 GEMM for sm_100a:  D[M,N] = A[M,K] · W[N,K]ᵀ, fp32 accumulate.
+// Persistent warp-specialised tcgen05 GEMM for sm_100a:  D[M,N] = A[M,K] * W[N,K]^T, fp32 accumulate.
 //
-//   warp 0      : TMA producer (one lane) — A and W tiles into a kStages-deep smem ring
-//   warp 1      : MMA issuer  (one lane) — tcgen05.mma, accumulators in TMEM (2 buffers)
+//   warp 0      : TMA producer (one lane) - A and W tiles into a kStages-deep smem ring
+//   warp 1      : MMA issuer  (one lane) - tcgen05.mma, accumulators in TMEM (2 buffers of 256 columns)
 //   warp 2      : TMEM allocator / deallocator
 //   warp 3      : idle
-//   warps 4..7  : epilogue — tcgen05.ld (one accumulator row per thread), fused functor, global store
+//   warps 4..7  : epilogue - tcgen05.ld (one accumulator row per thread), fused functor, global store
 //
 // Both operands are K-major 16-bit (bf16 or f16) staged with 128-byte swizzle; a tile is
 // 128 x BLOCK_N with K blocks of 64.  The A-side coordinates come from a "loader" policy so the
-// same kernel runs plain Linear layers (2-D tensor map) and the stride-2 3x3 convolutions of the
-// stem as implicit GEMM (4-D tensor map over parity-split NHWC planes, see stem.cuh).
+// same kernel runs the Linear layers (2-D tensor map) and the stride-2 3x3 convolutions of the
+// stem as implicit GEMM (4-D tensor map over parity-split channels-last planes, see stem.cuh).
 #pragma once
 #include "common.cuh"
 #include "tc.cuh"
@@ -40,25 +40,30 @@ struct LoaderLinear {
     __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m_blk, int kb) const {
         tc::tma_load_2d(dst, tmap, bar, kb * kBlockK, m_blk * kBlockM);
     }
-    __device__ __forceinline__ int b_k_coord(int kb) const { return kb * kBlockK; }
+    __device__ __forceinline__ int k_steps(int) const { return kBlockK / kUmmaK; }
 };
-// Conv (3x3, stride 2, pad 1) over parity-split planes: tensor map dims {C, Fh, R, 4 planes},
-// box {64, FW, 128/FW, 1}.  K index = tap*(c_blocks*64) + c, tap = dt*3 + df (dt: time, df: mel).
-//   dt=0 → odd-time plane, row R ; dt=1 → even-time plane, row R+1 ; dt=2 → odd-time plane, row R+1
-//   df=0 → odd-mel plane, col -1 ; df=1 → even-mel plane, col 0    ; df=2 → odd-mel plane, col 0
-// (every chunk's rows are preceded by one all-zero row, so "row R" of the odd plane is t = 2·ot-1.)
+// Conv (3x3, stride 2, pad 1) over parity-split planes (layout in stem.cuh): tensor map dims
+// {C, Fh, R, 4 planes}, box {64, Fh, 128/Fh, 1}.  Output row m = R_out * Fh + of where R_out indexes
+// (chunk, 1 + ot).  K index = tap * (c_blocks*64) + c, tap = dt*3 + df (dt: time tap, df: mel tap).
+//   dt=0 -> odd-time plane, row R_out-1 ; dt=1 -> even-time plane, row R_out ; dt=2 -> odd-time plane, row R_out
+//   df=0 -> odd-mel plane, col of-1     ; df=1 -> even-mel plane, col of     ; df=2 -> odd-mel plane, col of
+// Out-of-range coordinates (-1, or channels >= C in the last channel block) are zero-filled by TMA,
+// which is exactly the convolution's zero padding.
 struct LoaderConv {
     int num_k_blocks;       // 9 * c_blocks
     int c_blocks;           // ceil(C / 64)
-    int rows_per_tile;      // 128 / FW
+    int rows_per_tile;      // 128 / Fh
+    int last_block_steps;   // k-steps that hold real channels in the last channel block of a tap
     __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m_blk, int kb) const {
-        int tap = kb / c_blocks, cb = kb - tap * c_blocks;
-        int dt = tap / 3, df = tap - dt * 3;
-        int plane = ((dt != 1) ? 2 : 0) + ((df != 1) ? 1 : 0);
+        const int tap = kb / c_blocks, cb = kb - tap * c_blocks;
+        const int dt = tap / 3, df = tap - dt * 3;
+        const int plane = ((dt != 1) ? 2 : 0) + ((df != 1) ? 1 : 0);
         tc::tma_load_4d(dst, tmap, bar, cb * kBlockK, (df == 0) ? -1 : 0,
-                        m_blk * rows_per_tile + ((dt == 0) ? 0 : 1), plane);
+                        m_blk * rows_per_tile + ((dt == 0) ? -1 : 0), plane);
     }
-    __device__ __forceinline__ int b_k_coord(int kb) const { return kb * kBlockK; }
+    __device__ __forceinline__ int k_steps(int kb) const {
+        return ((kb % c_blocks) == c_blocks - 1) ? last_block_steps : kBlockK / kUmmaK;
+    }
 };
 
 // ---- the kernel ------------------------------------------------------------------------------
@@ -120,7 +125,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const uint32_t b_dst = a_dst + S::kABytes;
                     tc::mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
                     loader.load_a(a_dst, &tmap_a, full_bar(s), m_blk, kb);
-                    tc::tma_load_2d(b_dst, &tmap_b, full_bar(s), loader.b_k_coord(kb), n_blk * BLOCK_N);
+                    tc::tma_load_2d(b_dst, &tmap_b, full_bar(s), kb * kBlockK, n_blk * BLOCK_N);
                 }
             }
         }
@@ -144,10 +149,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const uint32_t b_addr = a_addr + S::kABytes;
                     const uint64_t a_desc = tc::smem_desc_kmajor_sw128(a_addr);
                     const uint64_t b_desc = tc::smem_desc_kmajor_sw128(b_addr);
+                    const int steps = loader.k_steps(kb);
 #pragma unroll
                     for (int k = 0; k < kBlockK / kUmmaK; ++k) {
                         // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
-                        tc::mma_f16_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                        if (k < steps) tc::mma_f16_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
                     }
                     tc::mma_commit(empty_bar(s));                      // frees the smem slot when the MMAs retire
                     if (kb == num_kb - 1) tc::mma_commit(tfull_bar(as));   // accumulator complete
@@ -155,8 +161,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 __syncwarp();
             }
         }
-    } else if (warp == 2) {
-        // allocator warp: nothing to do until teardown
     } else if (warp >= 4) {
         // ===================== epilogue =====================
         const int q = warp & 3;                       // TMEM lane quadrant this warp may read
