@@ -1,0 +1,22 @@
+// Varlen tcgen05 attention (attention.cu): host interface.
+#pragma once
+#include "common.cuh"
+
+namespace q3a {
+
+struct AttnTile {
+    int q0;          // first token row of this 128-query tile
+    int seg_start;   // tokens [seg_start, seg_end) attend to each other
+    int seg_end;
+    int pad;
+};
+
+// one tile per 128 queries of every segment; cu_seqlens has n_seg+1 ascending entries
+void attention_tiles(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& tiles);
+// 4 * head_dim * H * sum(len^2): QK^T and PV, 2 flops per MAC, no padding counted
+double attention_flops(const int* cu_seqlens, int n_seg, int n_heads);
+// qkv: [T][3*H*64] 16-bit (q | k | v column blocks), out: [T][H*64] 16-bit
+int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnTile* tiles_dev, int n_tiles, int fmt,
+                     cudaStream_t stream);
+
+}  // namespace q3a

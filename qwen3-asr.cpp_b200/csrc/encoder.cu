@@ -1,0 +1,715 @@
+// Audio-encoder forward for sm_100a: weight loading from GGUF and the launch sequence that replaces
+// AudioEncoder::encode / encode_no_chunk / encode_conv_only (reference audio_encoder.cpp:312-913) and
+// ForcedAligner::encode_audio (forced_aligner.cpp:591-924) for a packed batch of utterances.
+//
+//   stem       conv1 (CUDA cores) -> planes ; conv2, conv3 implicit GEMM (tcgen05) ; conv_out GEMM + PE
+//   18/24 x    LN -> fused QKV GEMM(+bias) -> varlen attention -> out GEMM(+bias,+residual)
+//              LN -> up GEMM(+bias, GELU) -> down GEMM(+bias,+residual)
+//   post       LN -> proj1 GEMM(+bias, GELU) -> proj2 GEMM(+bias) -> [T][out_dim] f32
+// The residual stream, LayerNorm statistics and softmax are fp32; tensor-core operands are 16-bit.
+#include "encoder.h"
+#include "gemm.h"
+#include "gguf_reader.h"
+#include "mel.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+namespace q3a {
+
+constexpr int kChunkFrames = 100;        // n_window * 2 (audio_encoder.cpp:327-328)
+constexpr int kWindowTokens = 104;       // 13 * (800 / 100) (forced_aligner.cpp:737-741)
+constexpr int kMaxChunksPerPass = 4096;  // bounds the stem workspace of the host-pointer entry points (~17 GB)
+
+int encoder_n_tokens(int n_frames, int mode) {
+    if (n_frames <= 0) return 0;
+    if (mode == Q3A_MODE_NO_CHUNK || mode == Q3A_MODE_CONV_ONLY) return stem_out_len(n_frames);
+    int total = (n_frames / kChunkFrames) * stem_out_len(kChunkFrames);
+    if (n_frames % kChunkFrames) total += stem_out_len(n_frames % kChunkFrames);
+    return total;
+}
+
+// ---- 16-bit conversion on the host ---------------------------------------------------------------
+static uint16_t to_op(float v, int fmt) {
+    if (fmt == OP_F16) { __half h = __float2half_rn(v); uint16_t u; std::memcpy(&u, &h, 2); return u; }
+    __nv_bfloat16 b = __float2bfloat16_rn(v);
+    uint16_t u; std::memcpy(&u, &b, 2);
+    return u;
+}
+
+// ---- weight arena ----------------------------------------------------------------------------------
+struct ArenaPlan {
+    struct Item { const void** slot; std::vector<uint8_t> bytes; };
+    std::vector<Item> items;
+    void add_f32(const float** slot, const std::vector<float>& v) {
+        Item it; it.slot = reinterpret_cast<const void**>(slot);
+        it.bytes.resize(v.size() * 4);
+        std::memcpy(it.bytes.data(), v.data(), it.bytes.size());
+        items.push_back(std::move(it));
+    }
+    void add_op(const void** slot, const std::vector<float>& v, int fmt) {
+        Item it; it.slot = slot;
+        it.bytes.resize(v.size() * 2);
+        uint16_t* d = reinterpret_cast<uint16_t*>(it.bytes.data());
+        for (size_t i = 0; i < v.size(); ++i) d[i] = to_op(v[i], fmt);
+        items.push_back(std::move(it));
+    }
+};
+
+static void sinusoidal_table(std::vector<float>& pe, int n_ctx, int d) {
+    // same float arithmetic as compute_sinusoidal_pe (audio_encoder.cpp:12-22)
+    const int half = d / 2;
+    pe.assign((size_t)n_ctx * d, 0.0f);
+    for (int i = 0; i < half; ++i) {
+        const float div_term = expf(-logf(10000.0f) * i / (half - 1));
+        for (int pos = 0; pos < n_ctx; ++pos) {
+            const float angle = pos * div_term;
+            pe[(size_t)pos * d + i] = sinf(angle);
+            pe[(size_t)pos * d + half + i] = cosf(angle);
+        }
+    }
+}
+
+static int ensure_pe(q3a_encoder* e, int rows, cudaStream_t st) {
+    if (rows <= e->pe_rows) return Q3A_OK;
+    rows = std::max(rows, 16);
+    std::vector<float> pe;
+    sinusoidal_table(pe, rows, e->hp.d_model);
+    Q3A_CUDA(cudaStreamSynchronize(st));          // nothing in flight may still read the old table
+    Q3A_TRY(e->pe.reserve(pe.size() * 4));
+    Q3A_CUDA(cudaMemcpy(e->pe.p, pe.data(), pe.size() * 4, cudaMemcpyHostToDevice));
+    e->pe_rows = rows;
+    return Q3A_OK;
+}
+
+// ---- profiling spans ---------------------------------------------------------------------------------
+enum SpanKind { SP_STEM = 0, SP_XFMR = 1, SP_GEMM = 2, SP_ATTN = 3, SP_OTHER = 4, SP_MEL = 5 };
+
+struct Prof {
+    q3a_encoder* e; cudaStream_t st;
+    int begin(int kind) {
+        if (!e->profiling) return -1;
+        while ((int)e->ev_pool.size() < e->ev_used + 2) {
+            cudaEvent_t ev; if (cudaEventCreate(&ev) != cudaSuccess) return -1;
+            e->ev_pool.push_back(ev);
+        }
+        const int i = e->ev_used; e->ev_used += 2;
+        cudaEventRecord(e->ev_pool[i], st);
+        e->spans.push_back({kind, i, i + 1});
+        return (int)e->spans.size() - 1;
+    }
+    void end(int span) { if (span >= 0) cudaEventRecord(e->ev_pool[e->spans[span].e1], st); }
+};
+
+static void prof_reset(q3a_encoder* e) {
+    e->spans.clear(); e->ev_used = 0;
+    e->tm = q3a_timings{};
+}
+
+static int prof_collect(q3a_encoder* e, cudaStream_t st) {
+    e->tm.total_launches = g_launch_counter;
+    if (!e->profiling) return Q3A_OK;
+    Q3A_CUDA(cudaStreamSynchronize(st));
+    for (const auto& s : e->spans) {
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, e->ev_pool[s.e0], e->ev_pool[s.e1]) != cudaSuccess) { cudaGetLastError(); continue; }
+        switch (s.kind) {
+            case SP_STEM: e->tm.conv_chunk_ms += ms; break;
+            case SP_XFMR: e->tm.transformer_ms += ms; break;
+            case SP_GEMM: e->tm.gemm_ms += ms; break;
+            case SP_ATTN: e->tm.attention_ms += ms; break;
+            case SP_MEL: e->tm.mel_ms += ms; break;
+            default: e->tm.other_ms += ms; break;
+        }
+    }
+    return Q3A_OK;
+}
+
+// ---- the forward pass --------------------------------------------------------------------------------
+template <class OpT>
+static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_off, const float* max_dev,
+                       const int* n_frames, int n_utts, int mode, float* out_dev, int64_t* tok_off_out,
+                       cudaStream_t st) {
+    const q3a_hparams& hp = e->hp;
+    const int d = hp.d_model, C = hp.conv_channels, H = hp.n_attention_heads, ffn = hp.ffn_dim;
+    const int fmt = e->fmt;
+    const bool chunked = (mode == Q3A_MODE_ASR || mode == Q3A_MODE_ALIGNER);
+    const bool pad_tail = (mode == Q3A_MODE_ALIGNER);
+    Prof prof{e, st};
+
+    // ---- host planning: chunks, token rows, attention segments ------------------------------------
+    std::vector<StemChunk> chunks;
+    std::vector<int> t2_valid, n_tok, tok_base, pos, cu;
+    std::vector<int64_t> tok_off(n_utts + 1, 0);
+    int T = 0, max_len = 0, max_pos = 0;
+    cu.push_back(0);
+    for (int u = 0; u < n_utts; ++u) {
+        tok_off[u] = T;
+        const int nf = n_frames[u];
+        if (nf < 0) { set_error("encode: negative n_frames"); return Q3A_ERR_ARG; }
+        const int step = chunked ? kChunkFrames : std::max(nf, 1);
+        const int t_utt0 = T;
+        for (int s = 0; s < nf; s += step) {
+            const int len = std::min(step, nf - s);
+            const int full = pad_tail ? kChunkFrames : len;       // frames the convolutions see
+            const int l1 = (full - 1) / 2 + 1, l2 = (l1 - 1) / 2 + 1;
+            StemChunk ck;
+            ck.mel_off = mel_off[u] + s; ck.row_stride = nf; ck.len = len; ck.t1_valid = l1; ck.utt = u;
+            chunks.push_back(ck);
+            t2_valid.push_back(l2);
+            const int nt = stem_out_len(len);
+            n_tok.push_back(nt);
+            tok_base.push_back(T);
+            for (int t = 0; t < nt; ++t) pos.push_back(t);
+            max_pos = std::max(max_pos, nt);
+            T += nt;
+            max_len = std::max(max_len, full);
+        }
+        if (mode == Q3A_MODE_ALIGNER) {
+            for (int s = t_utt0; s < T; s += kWindowTokens) cu.push_back(std::min(s + kWindowTokens, T));
+        } else if (T > t_utt0) {
+            cu.push_back(T);
+        }
+    }
+    tok_off[n_utts] = T;
+    if (tok_off_out) std::memcpy(tok_off_out, tok_off.data(), sizeof(int64_t) * (n_utts + 1));
+    const int n_chunks = (int)chunks.size();
+    if (T == 0) return Q3A_OK;
+    const int n_seg = (int)cu.size() - 1;
+    std::vector<AttnTile> tiles;
+    if (mode != Q3A_MODE_CONV_ONLY) attention_tiles(cu.data(), n_seg, tiles);
+
+    const int maxL1 = (max_len - 1) / 2 + 1;
+    const int P2 = 1 + (maxL1 + 1) / 2;           // rows per chunk of conv2's input planes / output row space
+    const int P3 = 1 + P2 / 2;                    // same for conv3
+    const int F2 = hp.n_mel_bins / 4, F3 = hp.n_mel_bins / 8;   // mel half-widths: 32, 16
+
+    // ---- tables: one pinned block -> one device block -------------------------------------------------
+    auto al = [](size_t v) { return (v + 255) / 256 * 256; };
+    const size_t o_chunks = 0;
+    const size_t o_t2 = al(o_chunks + sizeof(StemChunk) * n_chunks);
+    const size_t o_ntok = al(o_t2 + 4 * (size_t)n_chunks);
+    const size_t o_base = al(o_ntok + 4 * (size_t)n_chunks);
+    const size_t o_pos = al(o_base + 4 * (size_t)n_chunks);
+    const size_t o_tiles = al(o_pos + 4 * (size_t)T);
+    const size_t tab_bytes = al(o_tiles + sizeof(AttnTile) * tiles.size());
+    void* hraw = nullptr;
+    Q3A_TRY(e->ring.acquire(tab_bytes, &hraw));
+    uint8_t* hb = static_cast<uint8_t*>(hraw);
+    std::memcpy(hb + o_chunks, chunks.data(), sizeof(StemChunk) * n_chunks);
+    std::memcpy(hb + o_t2, t2_valid.data(), 4 * (size_t)n_chunks);
+    std::memcpy(hb + o_ntok, n_tok.data(), 4 * (size_t)n_chunks);
+    std::memcpy(hb + o_base, tok_base.data(), 4 * (size_t)n_chunks);
+    std::memcpy(hb + o_pos, pos.data(), 4 * (size_t)T);
+    if (!tiles.empty()) std::memcpy(hb + o_tiles, tiles.data(), sizeof(AttnTile) * tiles.size());
+    Q3A_TRY(e->tables.reserve(tab_bytes));
+    Q3A_CUDA(cudaMemcpyAsync(e->tables.p, hb, tab_bytes, cudaMemcpyHostToDevice, st));
+    Q3A_TRY(e->ring.mark(st));
+    const uint8_t* db = e->tables.as<uint8_t>();
+    const StemChunk* d_chunks = reinterpret_cast<const StemChunk*>(db + o_chunks);
+    const int* d_t2 = reinterpret_cast<const int*>(db + o_t2);
+    const int* d_ntok = reinterpret_cast<const int*>(db + o_ntok);
+    const int* d_base = reinterpret_cast<const int*>(db + o_base);
+    const int* d_pos = reinterpret_cast<const int*>(db + o_pos);
+    const AttnTile* d_tiles = reinterpret_cast<const AttnTile*>(db + o_tiles);
+
+    // ---- workspace ----------------------------------------------------------------------------------------
+    if (mode != Q3A_MODE_CONV_ONLY) Q3A_TRY(ensure_pe(e, max_pos, st));
+    const int r1 = n_chunks * P2, r2 = n_chunks * P3;
+    if (r1 > e->rcap1 || P2 != e->sigP2) {
+        const int cap = std::max(r1 + r1 / 4, e->rcap1);
+        Q3A_CUDA(cudaStreamSynchronize(st));
+        Q3A_TRY(e->planes1.reserve((size_t)4 * cap * F2 * C * 2));
+        Q3A_CUDA(cudaMemsetAsync(e->planes1.p, 0, (size_t)4 * cap * F2 * C * 2, st));
+        e->rcap1 = cap; e->sigP2 = P2;
+    }
+    if (r2 > e->rcap2 || P3 != e->sigP3) {
+        const int cap = std::max(r2 + r2 / 4, e->rcap2);
+        Q3A_CUDA(cudaStreamSynchronize(st));
+        Q3A_TRY(e->planes2.reserve((size_t)4 * cap * F3 * C * 2));
+        Q3A_CUDA(cudaMemsetAsync(e->planes2.p, 0, (size_t)4 * cap * F3 * C * 2, st));
+        e->rcap2 = cap; e->sigP3 = P3;
+    }
+    const int feat_dim = F3 * C;
+    Q3A_TRY(e->feat.reserve((size_t)T * feat_dim * 2));
+    if (mode != Q3A_MODE_CONV_ONLY) {
+        Q3A_TRY(e->x.reserve((size_t)T * d * 4));
+        Q3A_TRY(e->h.reserve((size_t)T * d * 2));
+        Q3A_TRY(e->qkv.reserve((size_t)T * 3 * d * 2));
+        Q3A_TRY(e->att.reserve((size_t)T * d * 2));
+        Q3A_TRY(e->up.reserve((size_t)T * ffn * 2));
+    }
+    OpT* planes1 = e->planes1.as<OpT>();
+    OpT* planes2 = e->planes2.as<OpT>();
+    const long long ps1 = (long long)e->rcap1 * F2 * C, ps2 = (long long)e->rcap2 * F3 * C;
+
+    // ---- stem -------------------------------------------------------------------------------------------------
+    const int sp_stem = prof.begin(SP_STEM);
+    {
+        const int sp = prof.begin(SP_OTHER);
+        Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks, n_chunks, P2, max_dev, e->conv1_w, e->conv1_b, C, planes1, ps1, st));
+        prof.end(sp);
+    }
+    {
+        ConvArgs a;
+        a.planes = planes1; a.R_cap = e->rcap1; a.R_used = r1; a.Fh = F2; a.C = C;
+        a.w = e->conv2_w; a.N = C; a.bias = e->conv2_b; a.P = P2;
+        a.out_planes = planes2; a.P_next = P3; a.out_plane_stride = ps2; a.ot_valid = d_t2;
+        const int sp = prof.begin(SP_GEMM);
+        Q3A_TRY(gemm_conv(false, fmt, a, st));
+        prof.end(sp);
+        double m = 0; for (int c = 0; c < n_chunks; ++c) m += (double)t2_valid[c] * F2;
+        e->tm.gemm_flops += 2.0 * m * C * 9.0 * C; ++e->tm.gemm_launches;
+    }
+    {
+        ConvArgs a;
+        a.planes = planes2; a.R_cap = e->rcap2; a.R_used = r2; a.Fh = F3; a.C = C;
+        a.w = e->conv3_w; a.N = C; a.bias = e->conv3_b; a.P = P3;
+        a.feat = e->feat.p; a.n_tok = d_ntok; a.tok_base = d_base;
+        const int sp = prof.begin(SP_GEMM);
+        Q3A_TRY(gemm_conv(true, fmt, a, st));
+        prof.end(sp);
+        e->tm.gemm_flops += 2.0 * (double)T * F3 * C * 9.0 * C; ++e->tm.gemm_launches;
+    }
+    auto linear = [&](EpiKind kind, const void* A, int K, const void* W, int N, void* out, const float* bias,
+                      const float* res, const float* pe_tab, const int* pos_tab) -> int {
+        LinearArgs a;
+        a.a = A; a.M = T; a.K = K; a.lda = K; a.w = W; a.N = N; a.ldw = K; a.out = out; a.ldc = N;
+        a.bias = bias; a.res = res; a.pe = pe_tab; a.pos = pos_tab;
+        const int sp = prof.begin(SP_GEMM);
+        const int rc = gemm_linear(kind, fmt, a, st);
+        prof.end(sp);
+        e->tm.gemm_flops += 2.0 * (double)T * N * K; ++e->tm.gemm_launches;
+        return rc;
+    };
+    if (mode == Q3A_MODE_CONV_ONLY) {
+        Q3A_TRY(linear(EPI_POSEMB_F32, e->feat.p, feat_dim, e->conv_out_w, d, out_dev, nullptr, nullptr, nullptr, nullptr));
+        prof.end(sp_stem);
+        return Q3A_OK;
+    }
+    float* x = e->x.as<float>();
+    Q3A_TRY(linear(EPI_POSEMB_F32, e->feat.p, feat_dim, e->conv_out_w, d, x, nullptr, nullptr, e->pe.as<float>(), d_pos));
+    prof.end(sp_stem);
+
+    // ---- transformer layers ---------------------------------------------------------------------------------
+    const int sp_x = prof.begin(SP_XFMR);
+    OpT* h = e->h.as<OpT>();
+    auto ln = [&](const float* g, const float* b) -> int {
+        const int sp = prof.begin(SP_OTHER);
+        const int rc = layernorm_launch<OpT>(x, g, b, hp.layer_norm_eps, T, d, h, st);
+        prof.end(sp);
+        return rc;
+    };
+    const double attn_fl = attention_flops(cu.data(), n_seg, H);
+    for (const auto& L : e->layers) {
+        Q3A_TRY(ln(L.ln1_g, L.ln1_b));
+        Q3A_TRY(linear(EPI_BIAS_OP, h, d, L.w_qkv, 3 * d, e->qkv.p, L.b_qkv, nullptr, nullptr, nullptr));
+        {
+            const int sp = prof.begin(SP_ATTN);
+            Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles, (int)tiles.size(), fmt, st));
+            prof.end(sp);
+            e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;
+        }
+        Q3A_TRY(linear(EPI_BIAS_RES_F32, e->att.p, d, L.w_o, d, x, L.b_o, x, nullptr, nullptr));
+        Q3A_TRY(ln(L.ln2_g, L.ln2_b));
+        Q3A_TRY(linear(EPI_BIAS_GELU_OP, h, d, L.w_up, ffn, e->up.p, L.b_up, nullptr, nullptr, nullptr));
+        Q3A_TRY(linear(EPI_BIAS_RES_F32, e->up.p, ffn, L.w_down, d, x, L.b_down, x, nullptr, nullptr));
+    }
+    Q3A_TRY(ln(e->lnp_g, e->lnp_b));
+    Q3A_TRY(linear(EPI_BIAS_GELU_OP, h, d, e->w_p1, d, e->att.p, e->b_p1, nullptr, nullptr, nullptr));
+    Q3A_TRY(linear(EPI_BIAS_F32, e->att.p, d, e->w_p2, hp.out_dim, out_dev, e->b_p2, nullptr, nullptr, nullptr));
+    prof.end(sp_x);
+    return Q3A_OK;
+}
+
+static int encode_dispatch(q3a_encoder* e, const float* mel_dev, const int64_t* mel_off, const float* max_dev,
+                           const int* n_frames, int n_utts, int mode, float* out_dev, int64_t* tok_off,
+                           cudaStream_t st) {
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
+    if (e->fmt == OP_F16)
+        return encode_core<__half>(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st);
+    return encode_core<__nv_bfloat16>(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st);
+}
+
+// ---- loading ------------------------------------------------------------------------------------------------
+static bool fetch(const GgufFile& f, const std::string& name, std::vector<float>& out, std::string& err,
+                  int64_t expect = -1) {
+    const GgufTensor* t = f.find(name);
+    if (!t) { err = "missing tensor " + name; return false; }
+    if (!f.read_f32(*t, out, err)) return false;
+    if (expect >= 0 && (int64_t)out.size() != expect) {
+        err = "tensor " + name + " has " + std::to_string(out.size()) + " elements, expected " + std::to_string(expect);
+        return false;
+    }
+    return true;
+}
+
+static int load_weights(q3a_encoder* e, const GgufFile& f) {
+    std::string err;
+    q3a_hparams& hp = e->hp;
+    const std::string P = "audio.encoder.";
+    // hyper-parameters: the keys the converter writes (convert_hf_to_gguf.py:441-447), else tensor shapes,
+    // else the reference defaults (gguf_loader.h:15-25)
+    const GgufTensor* t_co = f.find(P + "conv_out.weight");
+    const GgufTensor* t_c1 = f.find(P + "conv1.weight");
+    const GgufTensor* t_up = f.find(P + "blk.0.ffn_up.weight");
+    const GgufTensor* t_p2 = f.find(P + "proj2.weight");
+    if (!t_co || !t_c1 || !t_up || !t_p2 || t_co->ne.size() != 2 || t_c1->ne.size() != 4 || t_up->ne.size() != 2 ||
+        t_p2->ne.size() != 2) {
+        set_error("GGUF file has no audio.encoder.* tensors of the expected rank");
+        return Q3A_ERR_FORMAT;
+    }
+    int n_layers = 0;
+    while (f.find(P + "blk." + std::to_string(n_layers) + ".attn_q.weight")) ++n_layers;
+    const std::string A = "qwen3-asr.audio.";
+    hp.d_model = (int)f.get_u32(A + "encoder.embedding_length", (uint32_t)t_co->ne[1]);
+    hp.n_encoder_layers = (int)f.get_u32(A + "encoder.layer_count", (uint32_t)n_layers);
+    hp.ffn_dim = (int)f.get_u32(A + "encoder.feed_forward_length", (uint32_t)t_up->ne[1]);
+    hp.n_attention_heads = (int)f.get_u32(A + "encoder.attention.head_count", (uint32_t)(hp.d_model / 64));
+    hp.n_mel_bins = (int)f.get_u32(A + "num_mel_bins", 128);
+    hp.conv_channels = (int)f.get_u32(A + "conv_channels", (uint32_t)t_c1->ne[3]);
+    hp.conv_out_dim = hp.d_model;
+    hp.n_window_infer = 800;
+    hp.layer_norm_eps = 1e-5f;
+    hp.out_dim = (int)t_p2->ne[1];
+    hp.weight_ftype = (int)t_up->type;
+    const int d = hp.d_model, C = hp.conv_channels, ffn = hp.ffn_dim, F3 = hp.n_mel_bins / 8;
+    if (hp.n_mel_bins != 128) { set_error("only 128 mel bins are supported"); return Q3A_ERR_FORMAT; }
+    if (hp.n_attention_heads * 64 != d) { set_error("head_dim must be 64 (d_model = 64 * heads)"); return Q3A_ERR_FORMAT; }
+    if (d % 8 || ffn % 8 || C % 8 || hp.out_dim % 8 || d > 1024 || n_layers < hp.n_encoder_layers || d < 4) {
+        set_error("unsupported encoder shape (need multiples of 8, d_model <= 1024, all layers present)");
+        return Q3A_ERR_FORMAT;
+    }
+    if (t_co->ne[0] != (int64_t)C * F3) { set_error("conv_out.weight does not match conv_channels * 16"); return Q3A_ERR_FORMAT; }
+
+    ArenaPlan plan;
+    std::vector<float> v, v2, v3, packed;
+#define FETCH(name, vec, n) do { if (!fetch(f, P + (name), vec, err, (n))) { set_error(err); return Q3A_ERR_FORMAT; } } while (0)
+    // conv1: [C][1][3 mel][3 time] -> f32 [C][9] unchanged (index df*3 + dt)
+    FETCH("conv1.weight", v, (int64_t)C * 9);  plan.add_f32(&e->conv1_w, v);
+    FETCH("conv1.bias", v, C);                 plan.add_f32(&e->conv1_b, v);
+    // conv2/3: [OC][IC][3 mel (df)][3 time (dt)] -> [OC][tap = dt*3 + df][cpad] (gemm_tc.cuh LoaderConv)
+    const int cpad = (C + 63) / 64 * 64;
+    for (int ci = 2; ci <= 3; ++ci) {
+        FETCH("conv" + std::to_string(ci) + ".weight", v, (int64_t)C * C * 9);
+        packed.assign((size_t)C * 9 * cpad, 0.0f);
+        for (int oc = 0; oc < C; ++oc)
+            for (int ic = 0; ic < C; ++ic)
+                for (int df = 0; df < 3; ++df)
+                    for (int dt = 0; dt < 3; ++dt)
+                        packed[((size_t)oc * 9 + dt * 3 + df) * cpad + ic] = v[(((size_t)oc * C + ic) * 3 + df) * 3 + dt];
+        plan.add_op(ci == 2 ? &e->conv2_w : &e->conv3_w, packed, e->fmt);
+        FETCH("conv" + std::to_string(ci) + ".bias", v, C);
+        plan.add_f32(ci == 2 ? &e->conv2_b : &e->conv3_b, v);
+    }
+    // conv_out: [d][c*16 + f] (audio_encoder.cpp:139-142) -> [d][f*C + c] (the order conv3's epilogue writes)
+    FETCH("conv_out.weight", v, (int64_t)d * C * F3);
+    packed.assign(v.size(), 0.0f);
+    for (int n = 0; n < d; ++n)
+        for (int c = 0; c < C; ++c)
+            for (int ff = 0; ff < F3; ++ff) packed[(size_t)n * C * F3 + ff * C + c] = v[(size_t)n * C * F3 + c * F3 + ff];
+    plan.add_op(&e->conv_out_w, packed, e->fmt);
+
+    e->layers.assign(hp.n_encoder_layers, q3a_encoder::Layer{});
+    for (int l = 0; l < hp.n_encoder_layers; ++l) {
+        auto& L = e->layers[l];
+        const std::string B = "blk." + std::to_string(l) + ".";
+        FETCH(B + "attn_norm.weight", v, d); plan.add_f32(&L.ln1_g, v);
+        FETCH(B + "attn_norm.bias", v, d);   plan.add_f32(&L.ln1_b, v);
+        FETCH(B + "attn_q.weight", v, (int64_t)d * d);
+        FETCH(B + "attn_k.weight", v2, (int64_t)d * d);
+        FETCH(B + "attn_v.weight", v3, (int64_t)d * d);
+        packed = v; packed.insert(packed.end(), v2.begin(), v2.end()); packed.insert(packed.end(), v3.begin(), v3.end());
+        plan.add_op(&L.w_qkv, packed, e->fmt);
+        FETCH(B + "attn_q.bias", v, d); FETCH(B + "attn_k.bias", v2, d); FETCH(B + "attn_v.bias", v3, d);
+        packed = v; packed.insert(packed.end(), v2.begin(), v2.end()); packed.insert(packed.end(), v3.begin(), v3.end());
+        plan.add_f32(&L.b_qkv, packed);
+        FETCH(B + "attn_out.weight", v, (int64_t)d * d); plan.add_op(&L.w_o, v, e->fmt);
+        FETCH(B + "attn_out.bias", v, d);                plan.add_f32(&L.b_o, v);
+        FETCH(B + "ffn_norm.weight", v, d); plan.add_f32(&L.ln2_g, v);
+        FETCH(B + "ffn_norm.bias", v, d);   plan.add_f32(&L.ln2_b, v);
+        FETCH(B + "ffn_up.weight", v, (int64_t)ffn * d);   plan.add_op(&L.w_up, v, e->fmt);
+        FETCH(B + "ffn_up.bias", v, ffn);                  plan.add_f32(&L.b_up, v);
+        FETCH(B + "ffn_down.weight", v, (int64_t)d * ffn); plan.add_op(&L.w_down, v, e->fmt);
+        FETCH(B + "ffn_down.bias", v, d);                  plan.add_f32(&L.b_down, v);
+    }
+    FETCH("ln_post.weight", v, d); plan.add_f32(&e->lnp_g, v);
+    FETCH("ln_post.bias", v, d);   plan.add_f32(&e->lnp_b, v);
+    FETCH("proj1.weight", v, (int64_t)d * d);           plan.add_op(&e->w_p1, v, e->fmt);
+    FETCH("proj1.bias", v, d);                          plan.add_f32(&e->b_p1, v);
+    FETCH("proj2.weight", v, (int64_t)hp.out_dim * d);  plan.add_op(&e->w_p2, v, e->fmt);
+    FETCH("proj2.bias", v, hp.out_dim);                 plan.add_f32(&e->b_p2, v);
+#undef FETCH
+
+    size_t total = 0;
+    for (auto& it : plan.items) total += (it.bytes.size() + 255) / 256 * 256;
+    Q3A_TRY(e->arena.reserve(total));
+    size_t off = 0;
+    std::vector<uint8_t> host(total, 0);
+    for (auto& it : plan.items) {
+        std::memcpy(host.data() + off, it.bytes.data(), it.bytes.size());
+        *it.slot = e->arena.as<uint8_t>() + off;
+        off += (it.bytes.size() + 255) / 256 * 256;
+    }
+    Q3A_CUDA(cudaMemcpy(e->arena.p, host.data(), total, cudaMemcpyHostToDevice));
+    e->arena_used = total;
+    return Q3A_OK;
+}
+
+}  // namespace q3a
+
+using namespace q3a;
+
+// q3a_pack_offsets is defined in mel.cu
+int q3a_pack_offsets(const int* n, int count, int unit, int64_t align, std::vector<int64_t>& off);
+
+extern "C" void q3a_encoder_free(q3a_encoder* e) {
+    if (!e) return;
+    cudaSetDevice(e->device);
+    if (e->stream) cudaStreamSynchronize(e->stream);
+    e->arena.release(); e->pe.release();
+    e->planes1.release(); e->planes2.release(); e->feat.release(); e->x.release(); e->h.release(); e->qkv.release();
+    e->att.release(); e->up.release(); e->tables.release(); e->stage_in.release(); e->stage_out.release();
+    e->stage_mel.release(); e->stage_max.release();
+    e->ring.release();
+    for (auto ev : e->ev_pool) cudaEventDestroy(ev);
+    if (e->stream) cudaStreamDestroy(e->stream);
+    delete e;
+}
+
+extern "C" int q3a_encoder_load(const char* gguf_path, int device, int operand_dtype, q3a_encoder** out) {
+    if (!out) { set_error("encoder_load: out is null"); return Q3A_ERR_ARG; }
+    *out = nullptr;
+    if (!gguf_path) { set_error("encoder_load: path is null"); return Q3A_ERR_ARG; }
+    if (operand_dtype != Q3A_OP_BF16 && operand_dtype != Q3A_OP_F16) { set_error("encoder_load: unknown operand dtype"); return Q3A_ERR_ARG; }
+    GgufFile f;
+    std::string err;
+    if (!f.open(gguf_path, err)) {
+        set_error(err);
+        return (err.rfind("cannot open", 0) == 0 || err.rfind("cannot stat", 0) == 0 || err.rfind("mmap", 0) == 0) ? Q3A_ERR_IO : Q3A_ERR_FORMAT;
+    }
+    Q3A_TRY(use_device(device));
+    q3a_encoder* e = new q3a_encoder();
+    e->device = device; e->fmt = operand_dtype;
+    int rc = load_weights(e, f);
+    if (rc == Q3A_OK && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        set_error("cudaStreamCreate failed"); rc = Q3A_ERR_CUDA;
+    }
+    if (rc != Q3A_OK) { q3a_encoder_free(e); return rc; }
+    *out = e;
+    return Q3A_OK;
+}
+
+extern "C" int q3a_encoder_get_hparams(const q3a_encoder* e, q3a_hparams* out) {
+    if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (!out) { set_error("get_hparams: out is null"); return Q3A_ERR_ARG; }
+    *out = e->hp;
+    return Q3A_OK;
+}
+
+extern "C" int q3a_encoder_n_tokens(int n_frames, int mode) { return encoder_n_tokens(n_frames, mode); }
+
+extern "C" int q3a_encoder_set_profiling(q3a_encoder* e, int on) {
+    if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    e->profiling = on != 0;
+    return Q3A_OK;
+}
+
+extern "C" int q3a_encoder_get_timings(const q3a_encoder* e, q3a_timings* out) {
+    if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (!out) { set_error("get_timings: out is null"); return Q3A_ERR_ARG; }
+    *out = e->tm;
+    return Q3A_OK;
+}
+
+extern "C" int64_t q3a_encoder_device_bytes(const q3a_encoder* e) {
+    if (!e) return 0;
+    return (int64_t)(e->arena.cap + e->pe.cap + e->planes1.cap + e->planes2.cap + e->feat.cap + e->x.cap + e->h.cap +
+                     e->qkv.cap + e->att.cap + e->up.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap +
+                     e->stage_mel.cap + e->stage_max.cap);
+}
+
+extern "C" int q3a_encoder_encode_device(q3a_encoder* e, const float* mel_dev, const int64_t* mel_off,
+                                         const float* max_dev, const int* n_frames, int n_utts, int mode,
+                                         float* out_dev, int64_t* tok_off, void* stream) {
+    if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (n_utts < 0 || (n_utts > 0 && (!mel_dev || !mel_off || !n_frames || !out_dev))) { set_error("encode_device: null argument"); return Q3A_ERR_ARG; }
+    Q3A_TRY(use_device(e->device));
+    g_launch_counter = 0;
+    prof_reset(e);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    Q3A_TRY(encode_dispatch(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st));
+    return prof_collect(e, st);
+}
+
+// Splits [0, n) into passes whose stem workspace stays bounded.
+static void plan_passes(const int* n_frames, int n, int mode, std::vector<int>& bounds) {
+    bounds.assign(1, 0);
+    int chunks = 0;
+    for (int i = 0; i < n; ++i) {
+        const int c = (mode == Q3A_MODE_ASR || mode == Q3A_MODE_ALIGNER) ? (n_frames[i] + kChunkFrames - 1) / kChunkFrames
+                                                                          : (n_frames[i] + kChunkFrames - 1) / kChunkFrames + 1;
+        if (chunks > 0 && chunks + c > kMaxChunksPerPass) { bounds.push_back(i); chunks = 0; }
+        chunks += c;
+    }
+    bounds.push_back(n);
+}
+
+extern "C" int q3a_encoder_encode_batch(q3a_encoder* e, const float* const* mel, int n_mel, const int* n_frames,
+                                        int n_utts, int mode, float* const* out, int* n_tokens) {
+    if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (n_mel != e->hp.n_mel_bins) {
+        set_error("Mel bins mismatch: expected " + std::to_string(e->hp.n_mel_bins) + ", got " + std::to_string(n_mel));
+        return Q3A_ERR_ARG;
+    }
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
+    if (n_utts < 0 || (n_utts > 0 && (!mel || !n_frames || !out))) { set_error("encode_batch: null argument"); return Q3A_ERR_ARG; }
+    for (int u = 0; u < n_utts; ++u)
+        if (n_frames[u] < 0 || (n_frames[u] > 0 && (!mel[u] || !out[u]))) { set_error("encode_batch: bad utterance " + std::to_string(u)); return Q3A_ERR_ARG; }
+    Q3A_TRY(use_device(e->device));
+    g_launch_counter = 0;
+    prof_reset(e);
+    cudaStream_t st = e->stream;
+    const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
+    std::vector<int> bounds;
+    plan_passes(n_frames, n_utts, mode, bounds);
+    for (size_t p = 0; p + 1 < bounds.size(); ++p) {
+        const int u0 = bounds[p], nu = bounds[p + 1] - u0;
+        std::vector<int> elems(nu);
+        std::vector<int64_t> moff;
+        int T = 0;
+        for (int i = 0; i < nu; ++i) { elems[i] = n_mel * n_frames[u0 + i]; T += encoder_n_tokens(n_frames[u0 + i], mode); }
+        q3a_pack_offsets(elems.data(), nu, 1, 64, moff);
+        Q3A_TRY(e->stage_mel.reserve(sizeof(float) * (size_t)(moff[nu] + 64)));
+        Q3A_TRY(e->stage_out.reserve(sizeof(float) * ((size_t)T * width + 64)));
+        for (int i = 0; i < nu; ++i)
+            if (elems[i] > 0)
+                Q3A_CUDA(cudaMemcpyAsync(e->stage_mel.as<float>() + moff[i], mel[u0 + i], sizeof(float) * elems[i],
+                                         cudaMemcpyHostToDevice, st));
+        std::vector<int64_t> toff(nu + 1);
+        Q3A_TRY(encode_dispatch(e, e->stage_mel.as<float>(), moff.data(), nullptr, n_frames + u0, nu, mode,
+                                e->stage_out.as<float>(), toff.data(), st));
+        for (int i = 0; i < nu; ++i) {
+            const int64_t rows = toff[i + 1] - toff[i];
+            if (n_tokens) n_tokens[u0 + i] = (int)rows;
+            if (rows > 0)
+                Q3A_CUDA(cudaMemcpyAsync(out[u0 + i], e->stage_out.as<float>() + toff[i] * width,
+                                         sizeof(float) * rows * width, cudaMemcpyDeviceToHost, st));
+        }
+        Q3A_CUDA(cudaStreamSynchronize(st));
+    }
+    return prof_collect(e, st);
+}
+
+// mel (raw log10 + per-clip max) and encoder (clamp fused into conv1's loads) for clips on the device
+static int pcm_core(q3a_frontend* fe, q3a_encoder* e, const float* pcm_dev, const int64_t* pcm_off, const int* n_samples,
+                    int n_clips, int mode, float* out_dev, int64_t* tok_off, cudaStream_t st) {
+    if (fe->n_mel != e->hp.n_mel_bins) {
+        set_error("Mel bins mismatch: expected " + std::to_string(e->hp.n_mel_bins) + ", got " + std::to_string(fe->n_mel));
+        return Q3A_ERR_ARG;
+    }
+    if (fe->device != e->device) { set_error("frontend and encoder live on different devices"); return Q3A_ERR_ARG; }
+    std::vector<int> elems(n_clips), nf(n_clips);
+    std::vector<int64_t> moff;
+    for (int i = 0; i < n_clips; ++i) {
+        if (n_samples[i] < 0) { set_error("negative n_samples"); return Q3A_ERR_ARG; }
+        nf[i] = n_samples[i] / 160; elems[i] = fe->n_mel * nf[i];
+    }
+    q3a_pack_offsets(elems.data(), n_clips, 1, 64, moff);
+    Q3A_TRY(e->stage_mel.reserve(sizeof(float) * (size_t)(moff[n_clips] + 64)));
+    Q3A_TRY(e->stage_max.reserve(sizeof(float) * (size_t)(n_clips + 1)));
+    Prof prof{e, st};
+    const int sp = prof.begin(SP_MEL);
+    Q3A_TRY(mel_launch(fe, pcm_dev, pcm_off, n_samples, n_clips, e->stage_mel.as<float>(), moff.data(),
+                       e->stage_max.as<float>(), 0, st));
+    prof.end(sp);
+    return encode_dispatch(e, e->stage_mel.as<float>(), moff.data(), e->stage_max.as<float>(), nf.data(), n_clips, mode,
+                           out_dev, tok_off, st);
+}
+
+extern "C" int q3a_encode_pcm_device(q3a_frontend* fe, q3a_encoder* e, const float* pcm_dev, const int64_t* pcm_off,
+                                     const int* n_samples, int n_clips, int mode, float* out_dev, int64_t* tok_off,
+                                     void* stream) {
+    if (!e || !fe) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
+    if (n_clips < 0 || (n_clips > 0 && (!pcm_dev || !pcm_off || !n_samples || !out_dev))) { set_error("encode_pcm_device: null argument"); return Q3A_ERR_ARG; }
+    Q3A_TRY(use_device(e->device));
+    g_launch_counter = 0;
+    prof_reset(e);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    Q3A_TRY(pcm_core(fe, e, pcm_dev, pcm_off, n_samples, n_clips, mode, out_dev, tok_off, st));
+    return prof_collect(e, st);
+}
+
+extern "C" int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* e, const float* const* pcm, const int* n_samples,
+                                    int n_clips, int mode, float* const* out, int* n_tokens) {
+    if (!e || !fe) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
+    if (n_clips < 0 || (n_clips > 0 && (!pcm || !n_samples || !out))) { set_error("encode_pcm_batch: null argument"); return Q3A_ERR_ARG; }
+    for (int u = 0; u < n_clips; ++u)
+        if (n_samples[u] < 0 || (n_samples[u] > 0 && !pcm[u]) || (n_samples[u] >= 160 && !out[u])) {
+            set_error("encode_pcm_batch: bad clip " + std::to_string(u)); return Q3A_ERR_ARG;
+        }
+    Q3A_TRY(use_device(e->device));
+    g_launch_counter = 0;
+    prof_reset(e);
+    cudaStream_t st = e->stream;
+    const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
+    std::vector<int> nf(n_clips), bounds;
+    for (int i = 0; i < n_clips; ++i) nf[i] = n_samples[i] / 160;
+    plan_passes(nf.data(), n_clips, mode, bounds);
+    for (size_t p = 0; p + 1 < bounds.size(); ++p) {
+        const int u0 = bounds[p], nu = bounds[p + 1] - u0;
+        std::vector<int64_t> poff;
+        int T = 0;
+        for (int i = 0; i < nu; ++i) T += encoder_n_tokens(nf[u0 + i], mode);
+        q3a_pack_offsets(n_samples + u0, nu, 1, 64, poff);
+        Q3A_TRY(e->stage_in.reserve(sizeof(float) * (size_t)(poff[nu] + 64)));
+        Q3A_TRY(e->stage_out.reserve(sizeof(float) * ((size_t)T * width + 64)));
+        for (int i = 0; i < nu; ++i)
+            if (n_samples[u0 + i] > 0)
+                Q3A_CUDA(cudaMemcpyAsync(e->stage_in.as<float>() + poff[i], pcm[u0 + i], sizeof(float) * n_samples[u0 + i],
+                                         cudaMemcpyHostToDevice, st));
+        std::vector<int64_t> toff(nu + 1);
+        Q3A_TRY(pcm_core(fe, e, e->stage_in.as<float>(), poff.data(), n_samples + u0, nu, mode, e->stage_out.as<float>(),
+                         toff.data(), st));
+        for (int i = 0; i < nu; ++i) {
+            const int64_t rows = toff[i + 1] - toff[i];
+            if (n_tokens) n_tokens[u0 + i] = (int)rows;
+            if (rows > 0)
+                Q3A_CUDA(cudaMemcpyAsync(out[u0 + i], e->stage_out.as<float>() + toff[i] * width,
+                                         sizeof(float) * rows * width, cudaMemcpyDeviceToHost, st));
+        }
+        Q3A_CUDA(cudaStreamSynchronize(st));
+    }
+    return prof_collect(e, st);
+}
+
+// Longest-processing-time-first assignment.  Cost model: per token ~0.71 GFLOP of dense work plus the
+// attention term 4*64*H*L*len^2 (ASR constants); only the ratio between the two terms matters.
+extern "C" int q3a_plan_shards(const int* n_frames, int n_utts, int mode, int n_shards, int* shard_of) {
+    if (n_utts < 0 || n_shards <= 0 || (n_utts > 0 && (!n_frames || !shard_of))) { set_error("plan_shards: bad argument"); return Q3A_ERR_ARG; }
+    std::vector<double> cost(n_utts);
+    for (int i = 0; i < n_utts; ++i) {
+        const double T = encoder_n_tokens(n_frames[i], mode);
+        double seg2 = 0.0;
+        if (mode == Q3A_MODE_ALIGNER) {
+            const int full = (int)T / kWindowTokens, rem = (int)T % kWindowTokens;
+            seg2 = (double)full * kWindowTokens * kWindowTokens + (double)rem * rem;
+        } else seg2 = T * T;
+        cost[i] = 0.71e9 * T + 4.0 * 64 * 14 * 18 * seg2;
+    }
+    std::vector<int> order(n_utts);
+    std::iota(order.begin(), order.end(), 0);
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cost[a] > cost[b]; });
+    std::vector<double> load(n_shards, 0.0);
+    for (int i : order) {
+        int best = 0;
+        for (int s = 1; s < n_shards; ++s) if (load[s] < load[best]) best = s;
+        shard_of[i] = best;
+        load[best] += cost[i];
+    }
+    return Q3A_OK;
+}

@@ -1,0 +1,57 @@
+// Audio-encoder object (host side): resident weights, workspace and the launch sequence.
+#pragma once
+#include "common.cuh"
+#include "attention.h"
+#include "stem.h"
+
+#include <string>
+#include <vector>
+
+struct q3a_encoder {
+    int device = 0;
+    int fmt = q3a::OP_BF16;          // 16-bit operand type of every tensor-core kernel
+    q3a_hparams hp{};
+    cudaStream_t stream = nullptr;   // used by the host-pointer entry points
+
+    // ---- weights (one arena) -----------------------------------------------------------------
+    q3a::DevBuf arena;
+    size_t arena_used = 0;
+    const float *conv1_w = nullptr, *conv1_b = nullptr, *conv2_b = nullptr, *conv3_b = nullptr;
+    const void *conv2_w = nullptr, *conv3_w = nullptr, *conv_out_w = nullptr;
+    struct Layer {
+        const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_o, *b_up, *b_down;
+        const void *w_qkv, *w_o, *w_up, *w_down;
+    };
+    std::vector<Layer> layers;
+    const float *lnp_g = nullptr, *lnp_b = nullptr, *b_p1 = nullptr, *b_p2 = nullptr;
+    const void *w_p1 = nullptr, *w_p2 = nullptr;
+    q3a::DevBuf pe;                  // sinusoidal table [pe_rows][d_model] f32
+    int pe_rows = 0;
+
+    // ---- workspace (grows, never shrinks) -----------------------------------------------------
+    q3a::DevBuf planes1, planes2, feat, x, h, qkv, att, up, tables, stage_in, stage_out, stage_mel, stage_max;
+    int rcap1 = 0, rcap2 = 0, sigP2 = 0, sigP3 = 0;   // plane layout the zero rows were prepared for
+    q3a::PinnedRing ring;
+
+    // ---- profiling ------------------------------------------------------------------------------
+    bool profiling = false;
+    std::vector<cudaEvent_t> ev_pool;
+    struct Span { int kind; int e0, e1; };
+    std::vector<Span> spans;
+    int ev_used = 0;
+    q3a_timings tm{};
+    int launches_last = 0;
+};
+
+struct q3a_frontend;
+
+namespace q3a {
+
+// tokens of one stem chunk (audio_encoder.cpp:304-310)
+inline int stem_out_len(int n) {
+    for (int i = 0; i < 3; ++i) n = (n - 1) / 2 + 1;
+    return n;
+}
+int encoder_n_tokens(int n_frames, int mode);
+
+}  // namespace q3a
