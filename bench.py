@@ -1,0 +1,358 @@
+#!/usr/bin/env python
+"""bench.py — audio-seconds encoded per second through the log-mel frontend + audio encoder.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+A "step" is one pass of the hot path (q3a_encode_pcm_*: mel -> conv stem -> transformer layers ->
+projection) over one batch of 64 synthetic 30-s clips with random-init Qwen3-ASR-0.6B encoder weights
+(BASELINE.json configs[1]).  Every rank owns its own batch (utterance sharding, weak scaling, no
+collective on the compute path).  `value` is measured with the PCM resident in HBM (CUDA events on the
+launch stream); `e2e` goes through the host-pointer C-ABI call with pinned host buffers, H2D and D2H
+copies inside the timed region.  --impl reference times the CPU path (reference mel TU + the numpy
+restatement of the ggml encoder) on the box's host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "audio-sec encoded/sec (mel+encoder)"
+UNIT = "audio-s/s"
+CLIP_SECONDS = 30
+BATCH = 64
+SR = 16000
+ASR_GFLOP_PER_30S = 278.02
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm_gbs": float(d["hbm_gbs"]), "tflops_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                "tflops_burst": float(d["bf16_tflops"]), "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "tflops_sustained": 1400.0, "tflops_burst": 1590.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.stop_ev, self.th = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self.stop_ev.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self.stop_ev.wait(0.1)
+
+    def start(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+
+    def stop(self) -> dict:
+        self.stop_ev.set()
+        if self.th:
+            self.th.join(timeout=6)
+        sm, mx, reasons = [], 0.0, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = max(mx, float(r[1]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def ensure_gguf(tmpdir: str, ftype: str = "f16") -> str:
+    """Random-init ASR-0.6B encoder written the way the reference converter would (no checkpoints offline)."""
+    from q3a_b200 import synth
+    path = os.path.join(tmpdir, f"asr06b_seed0_{ftype}.gguf")
+    if not os.path.exists(path):
+        synth.write_gguf(path, synth.ASR_06B, synth.random_weights(synth.ASR_06B, 0), ftype)
+    return path
+
+
+# ------------------------------------------------------------------------------------------------ CPU arm
+_CPU_STATE = {}
+
+
+def _cpu_step(clip_s: float, seed: int):
+    """One clip through the CPU implementation of the path: mel through the reference's own translation
+    unit when oracle/_ref is present (single thread — the reference ignores n_threads,
+    mel_spectrogram.cpp:484-628), the encoder through the numpy restatement of the ggml graph (BLAS
+    threads = all host cores).  Returns (seconds total, seconds in mel)."""
+    from q3a_b200 import synth
+    from oracle import mel_oracle as MO, encoder_oracle as EO
+    st = _CPU_STATE
+    if not st:
+        shape = synth.ASR_06B
+        st["shape"] = shape
+        st["W"] = EO.Weights(synth.stored_weights(synth.random_weights(shape, 0), "f16"), "f16")
+        try:
+            st["ref"] = MO.RefMel(); st["filt"] = st["ref"].filters()
+            st["mel_kind"] = "reference TU mel_spectrogram.cpp (1 thread)"
+        except Exception:
+            st["ref"] = None; st["filt"] = MO.mel_filters_numpy()
+            st["mel_kind"] = "numpy restatement (oracle/_ref missing)"
+    pcm = synth.synth_audio(seed, int(clip_s * SR))
+    t0 = time.perf_counter()
+    mel = st["ref"].log_mel(pcm, st["filt"]) if st["ref"] else MO.log_mel_numpy(pcm, st["filt"])
+    t1 = time.perf_counter()
+    sh = st["shape"]
+    EO.encode(mel, st["W"], n_layers=sh.n_layers, d_model=sh.d_model, n_heads=sh.n_heads, variant="asr")
+    t2 = time.perf_counter()
+    return t2 - t0, t1 - t0
+
+
+def cpu_path_rate(clip_seconds: float, n_clips: int, seed0: int = 100):
+    """Bounded CPU sample -> (audio-s/s, description for the cpu_baseline object)."""
+    tot = mel = 0.0
+    for i in range(n_clips):
+        a, b = _cpu_step(clip_seconds, seed0 + i)
+        tot += a; mel += b
+    desc = {"kind": "port", "cores": os.cpu_count() or 1,
+            "sample": f"{n_clips} x {clip_seconds:g}-s clips; mel: {_CPU_STATE['mel_kind']} ({mel:.1f} s); encoder: numpy "
+                      f"restatement of the ggml graph, f16 weights, BLAS on all cores ({tot - mel:.1f} s)"}
+    return n_clips * clip_seconds / tot, desc
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    total = args.steps + args.warmup
+    clip_s = 30.0 if total <= 16 else (10.0 if total <= 48 else 5.0)
+    t_all = time.perf_counter()
+    secs = mel = 0.0
+    for i in range(total):
+        a, b = _cpu_step(clip_s, 100 + i)
+        if i >= args.warmup:
+            secs += a; mel += b
+    value = args.steps * clip_s / secs
+    desc = {"kind": "port", "cores": os.cpu_count() or 1,
+            "sample": f"{args.steps} x {clip_s:g}-s clips; mel: {_CPU_STATE['mel_kind']} ({mel:.1f} s); encoder: numpy "
+                      f"restatement of the ggml graph, f16 weights, BLAS on all cores ({secs - mel:.1f} s)"}
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f16 weights, f32/f64 arithmetic", "data": "synthetic",
+            "config": {"workload": f"qwen3-asr-0.6b mel+encoder, one {clip_s:g}-s synthetic clip per step, CPU host cores",
+                       "clip_seconds": clip_s},
+            "cpu_baseline": {"value": value, "unit": UNIT, **desc},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0, "wall_s": time.perf_counter() - t_all}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import q3a_b200  # noqa: F401
+    from q3a_b200 import binding as B, synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B.load()
+
+    tmpdir = os.path.join(tempfile.gettempdir(), "q3a_bench")
+    os.makedirs(tmpdir, exist_ok=True)
+    if rank == 0:
+        ensure_gguf(tmpdir)
+    if world > 1:
+        dist.barrier()
+    gguf_path = ensure_gguf(tmpdir)
+    fe = B.Frontend(local)
+    enc = B.Encoder(gguf_path, local, B.OP_BF16)
+
+    n = CLIP_SECONDS * SR
+    # two input sets per rank, alternated between steps (2 x 123 MB PCM > the 126 MB L2; the ~8 GB of
+    # workspace a step streams through evicts everything anyway)
+    sets = []
+    for s in range(2):
+        base = synth.synth_audio(1000 + 17 * rank + s, n)
+        host = torch.empty((BATCH, n), dtype=torch.float32).pin_memory()
+        rng = np.random.default_rng(5000 + 131 * rank + s)
+        hv = host.numpy()
+        for i in range(BATCH):                       # distinct clips: circular shift + gain of a synthetic utterance
+            hv[i] = np.roll(base, int(rng.integers(0, n))) * np.float32(rng.uniform(0.5, 1.0))
+        sets.append(host)
+    dev_sets = [h.cuda() for h in sets]
+    pcm_off = [i * n for i in range(BATCH)]
+    n_samples = [n] * BATCH
+    T = enc.n_tokens(n // 160) * BATCH
+    out_dev = torch.empty((T, enc.hp.out_dim), dtype=torch.float32, device="cuda")
+    out_host = [torch.empty((T // BATCH, enc.hp.out_dim), dtype=torch.float32).pin_memory() for _ in range(BATCH)]
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_dev(i):
+        enc.encode_pcm_device(fe, dev_sets[i & 1].data_ptr(), pcm_off, n_samples, out_dev.data_ptr(), B.MODE_ASR, stream)
+
+    import ctypes as C
+    outs_ptr = (C.c_void_p * BATCH)(*[o.data_ptr() for o in out_host])
+    ns_arr = (C.c_int * BATCH)(*n_samples)
+    ntok = (C.c_int * BATCH)()
+    pcm_ptrs = [(C.c_void_p * BATCH)(*[h[i].data_ptr() for i in range(BATCH)]) for h in sets]
+
+    def step_e2e(i):
+        B.check(enc.lib.q3a_encode_pcm_batch(fe.h, enc.h, pcm_ptrs[i & 1], ns_arr, BATCH, B.MODE_ASR, outs_ptr, ntok))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing ----------------------------------------------------------------------
+    for i in range(args.warmup):
+        step_dev(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = 0
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step_dev(i)
+        launches0 += enc.timings().total_launches
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    audio_s = BATCH * CLIP_SECONDS * args.steps * world
+    value = audio_s / (ms_total / 1e3)
+
+    # ---- end-to-end through the host-pointer C ABI -------------------------------------------------------
+    for i in range(max(1, min(args.warmup, 3))):
+        step_e2e(i)
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        step_e2e(i)
+    torch.cuda.synchronize()
+    dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    e2e_value = audio_s / float(dt.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0: per-kernel roofline from a profiled pass of the same steps (events inside the library,
+    #      on the launch stream), parity smoke, CPU baseline ---------------------------------------------
+    pk = peaks()
+    enc.set_profiling(True)
+    g_ms = g_fl = a_ms = a_fl = mel_ms = stem_ms = x_ms = 0.0
+    g_n = 0
+    for i in range(args.steps):
+        step_dev(i)
+        tm = enc.timings()
+        g_ms += tm.gemm_ms; g_fl += tm.gemm_flops; a_ms += tm.attention_ms; a_fl += tm.attention_flops
+        mel_ms += tm.mel_ms; stem_ms += tm.conv_chunk_ms; x_ms += tm.transformer_ms; g_n += tm.gemm_launches
+    enc.set_profiling(False)
+    gemm_tf = g_fl / g_ms / 1e9
+    mel_bytes = BATCH * (4 * n + 4 * 128 * (n // 160)) * args.steps
+    mel_gbs = mel_bytes / (mel_ms / 1e3) / 1e9
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tp):
+        try:
+            with open(tp) as f:
+                traffic = json.load(f).get("gemm_tc_kernel_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        v, desc = cpu_path_rate(30.0, 2)
+        cpu = {"value": v, "unit": UNIT, **desc}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16 operands, fp32 accumulate (mel: fp32)", "data": "synthetic",
+        "config": {"workload": "qwen3-asr-0.6b mel+encoder, batch of 64 x 30-s synthetic 16 kHz clips per GPU "
+                               "(BASELINE.json configs[1]), random-init weights via GGUF F16",
+                   "batch_clips": BATCH, "clip_seconds": CLIP_SECONDS, "tokens_per_step": T, "mode": "asr (full attention)",
+                   "l2": "two PCM input sets alternated (246 MB > L2); a step streams ~8 GB of workspace",
+                   "algorithmic_gflop_per_step": ASR_GFLOP_PER_30S * BATCH},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * n * 4,
+                "d2h_bytes_per_step": T * enc.hp.out_dim * 4, "timer": "host wall clock around K synchronous C-ABI calls, max over ranks",
+                "api": "q3a_encode_pcm_batch (pinned host PCM -> pinned host features)"},
+        "gpu_launches": launches0,
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM: conv2/conv3 implicit GEMM + all Linear layers)",
+                     "achieved": gemm_tf, "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": gemm_tf / pk["tflops_sustained"],
+                     "traffic": traffic, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                     "launches_per_step": g_n // max(args.steps, 1), "ms_per_step": g_ms / args.steps,
+                     "how": "algorithmic FLOPs (2*M*N*K, no padding) / CUDA-event time of every launch, separate profiled pass of the same K steps"},
+        "roofline_attention": {"bound": "tensor", "kernel": "attention_kernel (tcgen05 varlen attention)",
+                               "achieved": a_fl / a_ms / 1e9, "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
+                               "frac": a_fl / a_ms / 1e9 / pk["tflops_sustained"], "ms_per_step": a_ms / args.steps},
+        "roofline_mel": {"bound": "hbm", "kernel": "mel_frames_kernel (+ max decode)", "achieved": mel_gbs, "peak": pk["hbm_gbs"],
+                         "unit": "GB/s", "frac": mel_gbs / pk["hbm_gbs"], "ms_per_step": mel_ms / args.steps,
+                         "how": "(4*n_samples + 4*128*n_len) per clip / CUDA-event time"},
+        "stage_ms_per_step": {"mel_spectrogram": mel_ms / args.steps, "audio_encoding.conv_chunk": stem_ms / args.steps,
+                              "audio_encoding.transformer": x_ms / args.steps},
+        "whole_step_tflops": ASR_GFLOP_PER_30S * BATCH * args.steps * world / (ms_total / 1e3) / 1e3,
+        "device_bytes": enc.device_bytes(),
+    }
+    if cpu is not None:
+        line["cpu_baseline"] = cpu
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~20 s CPU baseline leg (profiling runs)")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,89 @@
+"""The C-ABI library on a box without a GPU: it loads, exports every symbol include/q3a.h declares, its
+host-only entry points agree with the reference/oracle, and compute entry points fail loudly
+(there is no CPU fallback)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from q3a_b200 import binding as B, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_exports_every_declared_symbol(lib):
+    with open(os.path.join(ROOT, "include", "q3a.h")) as f:
+        header = f.read()
+    declared = set(re.findall(r"\b(q3a_[a-z0-9_]+)\s*\(", header))
+    assert len(declared) >= 20
+    assert declared == set(B.SYMBOLS), declared ^ set(B.SYMBOLS)
+    for name in declared:
+        assert hasattr(lib, name), name
+    assert lib.q3a_version() >= 100
+
+
+def test_generate_mel_filters_matches_reference_golden(lib):
+    g = np.load(os.path.join(ROOT, "tests", "golden", "mel_ref.npz"))
+    bank = B.generate_mel_filters()
+    assert np.abs(bank - g["filters"]).max() <= 1e-7
+    assert int((bank != 0).sum()) == 396
+
+
+def test_frame_and_token_counts(lib):
+    for n in (0, 1, 159, 160, 16000, 480000, 480001, 1472000):
+        assert lib.q3a_mel_n_len(n) == n // 160 == synth.mel_frames(n)
+    for nf in (0, 1, 99, 100, 101, 237, 3000, 9200, 12000):
+        assert lib.q3a_encoder_n_tokens(nf, B.MODE_ASR) == synth.chunk_tokens(nf)
+        assert lib.q3a_encoder_n_tokens(nf, B.MODE_ALIGNER) == synth.chunk_tokens(nf)
+    assert lib.q3a_encoder_n_tokens(3000, B.MODE_NO_CHUNK) == 375      # one 3000-frame chunk: 1500 -> 750 -> 375
+
+
+def test_plan_shards_is_balanced_and_deterministic(lib):
+    rng = np.random.default_rng(500)
+    frames = [int(x) for x in np.exp(rng.uniform(np.log(200), np.log(6000), 400))]
+    a = B.plan_shards(frames, B.MODE_ASR, 8)
+    assert a == B.plan_shards(frames, B.MODE_ASR, 8)
+    assert set(a) == set(range(8))
+    cost = np.array([synth.chunk_tokens(f) for f in frames], dtype=np.float64)
+    cost = 0.71e9 * cost + 4 * 64 * 14 * 18 * cost ** 2
+    loads = np.array([cost[np.array(a) == s].sum() for s in range(8)])
+    assert loads.max() / loads.mean() < 1.02
+    assert B.plan_shards([], B.MODE_ASR, 4) == []
+    with pytest.raises(B.Q3AError):
+        B.plan_shards(frames, B.MODE_ASR, 0)
+
+
+def test_loader_error_codes(lib, tmp_path):
+    h = C.c_void_p()
+    rc = lib.q3a_encoder_load(str(tmp_path / "missing.gguf").encode(), 0, B.OP_BF16, C.byref(h))
+    assert rc == 3 and b"cannot open" in lib.q3a_last_error()          # Q3A_ERR_IO
+    bad = tmp_path / "bad.gguf"
+    bad.write_bytes(b"NOPE" + bytes(64))
+    rc = lib.q3a_encoder_load(str(bad).encode(), 0, B.OP_BF16, C.byref(h))
+    assert rc == 4 and b"magic" in lib.q3a_last_error()                 # Q3A_ERR_FORMAT
+    rc = lib.q3a_encoder_load(str(bad).encode(), 0, 7, C.byref(h))
+    assert rc == 1                                                       # Q3A_ERR_ARG
+    assert not h.value
+
+
+def test_null_handles_report_model_not_loaded(lib):
+    hp = B.HParams()
+    assert lib.q3a_encoder_get_hparams(None, C.byref(hp)) == 5           # Q3A_ERR_STATE
+    assert b"Model not loaded" in lib.q3a_last_error()                   # audio_encoder.cpp:316-319
+    assert lib.q3a_encoder_encode_batch(None, None, 128, None, 0, 0, None, None) == 5
+    lib.q3a_encoder_free(None)
+    lib.q3a_frontend_free(None)
+
+
+def test_compute_fails_loudly_without_gpu(lib, tiny_models):
+    if lib.q3a_device_count() > 0:
+        pytest.skip("a B200 is present")
+    fe = C.c_void_p()
+    assert lib.q3a_frontend_create(0, None, 0, 0, C.byref(fe)) == 2      # Q3A_ERR_CUDA
+    assert b"no CPU fallback" in lib.q3a_last_error()
+    _, models = tiny_models
+    h = C.c_void_p()
+    assert lib.q3a_encoder_load(models["f16"][0].encode(), 0, B.OP_BF16, C.byref(h)) == 2
+    assert not h.value

