@@ -1,0 +1,122 @@
+#!/usr/bin/env python
+"""Turns the ncu outputs a GPU visit leaves in gpurun_out/ into the tracked summaries under profiles/.
+
+    python scripts/summarize_profile.py <tag>      # e.g. r1a  -> profiles/<tag>_launches.md, <tag>_kernels.csv
+
+Inputs (all optional): gpurun_out/launches.csv (the `--metrics gpu__time_duration.sum` pass),
+gpurun_out/prof_*.ncu-rep (`--set full` captures), gpurun_out/bench.json.
+"""
+from __future__ import annotations
+
+import collections
+import csv
+import glob
+import io
+import json
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GO = os.path.join(ROOT, "gpurun_out")
+PROF = os.path.join(ROOT, "profiles")
+
+RAW_METRICS = [
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
+    "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
+]
+
+
+def short_name(full: str) -> str:
+    s = re.sub(r"^void ", "", full)
+    s = s.replace("q3a::", "").replace("__nv_bfloat16", "bf16").replace("__half", "f16")
+    s = re.sub(r"\((?:const |CUtensorMap_st|float|int|unsigned|long|T\d).*$", "", s)
+    return s
+
+
+def launches(tag: str) -> None:
+    path = os.path.join(GO, "launches.csv")
+    if not os.path.exists(path):
+        return
+    rows = list(csv.reader(open(path, newline="")))
+    hi = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
+    hdr = rows[hi]
+    kn, mv, gs, bs = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size"), hdr.index("Block Size")
+    agg: dict = collections.OrderedDict()
+    total = 0.0
+    n = 0
+    for r in rows[hi + 1:]:
+        if len(r) <= mv:
+            continue
+        ns = float(r[mv].replace(",", ""))
+        key = (short_name(r[kn]), r[gs], r[bs])
+        a = agg.setdefault(key, [0, 0.0])
+        a[0] += 1
+        a[1] += ns
+        total += ns
+        n += 1
+    with open(os.path.join(PROF, f"{tag}_launches.md"), "w") as f:
+        f.write(f"# ncu launch list — {tag}\n\n")
+        f.write("`ncu --metrics gpu__time_duration.sum --clock-control none` over whole steps of `bench.py` "
+                "(64 x 30-s clips, ASR-0.6B, bf16 operands).  Times are cold-cache and serialised: compare shares.\n\n")
+        f.write(f"{n} launches, {total / 1e6:.3f} ms in total.\n\n")
+        f.write("| kernel | grid | block | launches | total ms | share | mean us |\n|---|---|---|---:|---:|---:|---:|\n")
+        for (name, g, b), (cnt, ns) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write(f"| `{name}` | {g} | {b} | {cnt} | {ns / 1e6:.3f} | {100 * ns / total:.1f}% | {ns / cnt / 1e3:.1f} |\n")
+    print("wrote", f"profiles/{tag}_launches.md")
+
+
+def full_reports(tag: str) -> None:
+    out_rows = []
+    for rep in sorted(glob.glob(os.path.join(GO, "prof_*.ncu-rep"))):
+        r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
+        if r.returncode != 0:
+            print("ncu -i failed on", rep, r.stderr[:200])
+            continue
+        rows = list(csv.reader(io.StringIO(r.stdout)))
+        hdr = rows[0]
+        col = {h: i for i, h in enumerate(hdr)}
+        for row in rows[2:]:
+            d = {"report": os.path.basename(rep), "kernel": short_name(row[col["Kernel Name"]])}
+            for m in RAW_METRICS:
+                if m in col:
+                    d[m] = row[col[m]]
+            out_rows.append(d)
+    if not out_rows:
+        return
+    keys = ["report", "kernel"] + RAW_METRICS
+    with open(os.path.join(PROF, f"{tag}_kernels.csv"), "w", newline="") as f:
+        w = csv.DictWriter(f, fieldnames=keys)
+        w.writeheader()
+        for d in out_rows:
+            w.writerow({k: d.get(k, "") for k in keys})
+    print("wrote", f"profiles/{tag}_kernels.csv")
+
+
+def bench(tag: str) -> None:
+    for name in ("bench.json", "bench_ref.json"):
+        p = os.path.join(GO, name)
+        if os.path.exists(p) and os.path.getsize(p) > 0:
+            with open(p) as f:
+                txt = f.read().strip().splitlines()[-1]
+            try:
+                json.loads(txt)
+            except Exception:
+                continue
+            with open(os.path.join(PROF, f"{tag}_{name}"), "w") as f:
+                f.write(txt + "\n")
+            print("wrote", f"profiles/{tag}_{name}")
+
+
+if __name__ == "__main__":
+    tag = sys.argv[1] if len(sys.argv) > 1 else "r1"
+    os.makedirs(PROF, exist_ok=True)
+    launches(tag)
+    full_reports(tag)
+    bench(tag)
