@@ -1,5 +1,5 @@
 // Fused epilogues for gemm_tc_kernel: each thread owns one output row and gets 32 consecutive
-// fp32 accumulator columns at a time (see the contract in gemm_tc.cuh).
+// fp32 accumulator columns at a time (see the two contracts in gemm_tc.cuh).
 #pragma once
 #include "common.cuh"
 
@@ -24,49 +24,45 @@ __device__ __forceinline__ void store8_f32(float* p, const float (&v)[8]) {
     *(reinterpret_cast<float4*>(p) + 1) = make_float4(v[4], v[5], v[6], v[7]);
 }
 
+// ---- staged epilogues (Linear layers): the kernel stores v through smem + TMA ---------------------
 // out[m][n] = act(acc + bias[n])  -> 16-bit operand for the next GEMM
 template <class OpT, bool kGelu>
 struct EpiBiasActOp {
-    OpT* out; int ldc; const float* bias;
-    __device__ __forceinline__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const {
-        OpT* row = out + (size_t)m * ldc + n0;
+    static constexpr bool kStaged = true, kResidual = false;
+    static constexpr int kOutBytes = 2;
+    const float* bias;
+    __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float b[8], v[8];
+                float b[8];
                 if (bias) load8(bias + n0 + g * 8, b);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    float x = acc[g * 8 + j] + (bias ? b[j] : 0.0f);
-                    v[j] = kGelu ? gelu_tanh(x) : x;
+                    float x = v[g * 8 + j] + (bias ? b[j] : 0.0f);
+                    v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
                 }
-                store8_op<OpT>(row + g * 8, v);
             }
         }
     }
 };
 
-// out[m][n] = acc + bias[n] (+ res[m][n])  -> fp32 (residual stream / final features); res may alias out
-template <bool kResidual>
+// out[m][n] = acc + bias[n] (+ out[m][n])  -> fp32 (residual stream updated in place / final features)
+template <bool kRes>
 struct EpiBiasF32 {
-    float* out; int ldc; const float* bias; const float* res;
-    __device__ __forceinline__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const {
-        float* row = out + (size_t)m * ldc + n0;
-        const float* rrow = kResidual ? res + (size_t)m * ldc + n0 : nullptr;
+    static constexpr bool kStaged = true, kResidual = kRes;
+    static constexpr int kOutBytes = 4;
+    const float* bias;
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
+        if (!bias) return;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float b[8], r[8], v[8];
-                if (bias) load8(bias + n0 + g * 8, b);
-                if (kResidual) {
-                    float4 a0 = *reinterpret_cast<const float4*>(rrow + g * 8);
-                    float4 a1 = *(reinterpret_cast<const float4*>(rrow + g * 8) + 1);
-                    r[0] = a0.x; r[1] = a0.y; r[2] = a0.z; r[3] = a0.w; r[4] = a1.x; r[5] = a1.y; r[6] = a1.z; r[7] = a1.w;
-                }
+                float b[8];
+                load8(bias + n0 + g * 8, b);
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    v[j] = acc[g * 8 + j] + (bias ? b[j] : 0.0f) + (kResidual ? r[j] : 0.0f);
-                store8_f32(row + g * 8, v);
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] += b[j];
             }
         }
     }
@@ -75,18 +71,19 @@ struct EpiBiasF32 {
 // conv_out: x[m][n] = acc + pe[pos[m]][n]   (sinusoidal table restarts per stem chunk,
 // audio_encoder.cpp:400-404 / forced_aligner.cpp:718-735); pe == nullptr -> plain store (conv-only mode)
 struct EpiPosEmbF32 {
-    float* out; int ldc; const float* pe; const int* pos;
-    __device__ __forceinline__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const {
-        float* row = out + (size_t)m * ldc + n0;
-        const float* prow = pe ? pe + (size_t)__ldg(pos + m) * ldc + n0 : nullptr;
+    static constexpr bool kStaged = true, kResidual = false;
+    static constexpr int kOutBytes = 4;
+    const float* pe; const int* pos; int ld; int M;
+    __device__ __forceinline__ void apply(int m, int n0, int nvalid, float (&v)[32]) const {
+        if (!pe || m >= M) return;
+        const float* prow = pe + (size_t)__ldg(pos + m) * ld + n0;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float p[8], v[8];
-                if (pe) load8(prow + g * 8, p);
+                float p[8];
+                load8(prow + g * 8, p);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[j] = acc[g * 8 + j] + (pe ? p[j] : 0.0f);
-                store8_f32(row + g * 8, v);
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] += p[j];
             }
         }
     }
@@ -99,6 +96,8 @@ struct EpiPosEmbF32 {
 // convolution's zero padding instead of stale data.
 template <class OpT>
 struct EpiConvToPlanes {
+    static constexpr bool kStaged = false, kResidual = false;
+    static constexpr int kOutBytes = 4;
     OpT* planes;            // next conv's input: [4][R_cap_next][OF/2][C]
     const float* bias;
     const int* ot_valid;    // per chunk: valid output time steps of this conv
@@ -131,6 +130,8 @@ struct EpiConvToPlanes {
 // order is channel*16 + of, audio_encoder.cpp:139-142).  Only the tokens the mode keeps are written.
 template <class OpT>
 struct EpiConvToFeat {
+    static constexpr bool kStaged = false, kResidual = false;
+    static constexpr int kOutBytes = 4;
     OpT* feat;              // [tokens][OF*C]
     const float* bias;
     const int* n_tok;       // per chunk: tokens kept

@@ -46,4 +46,12 @@ int gemm_conv(bool to_feat, int fmt, const ConvArgs& a, cudaStream_t stream);
 int pick_block_n(int N);
 int sm_count();
 
+// one-time (cached per kernel and device) setup of a gemm_tc_kernel instantiation: opt in to its dynamic shared memory
+// and ask how many CTA pairs (clusters of 2) can be resident at once -> persistent grid size
+int gemm_prepare_impl(const void* kernel, int smem_bytes, int threads, int* max_pairs);
+template <class Kern>
+int gemm_prepare(Kern kern, int smem_bytes, int* max_pairs) {
+    return gemm_prepare_impl(reinterpret_cast<const void*>(kern), smem_bytes, 384, max_pairs);
+}
+
 }  // namespace q3a

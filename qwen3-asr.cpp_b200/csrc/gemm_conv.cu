@@ -11,7 +11,7 @@ namespace q3a {
 
 template <int BLOCK_N, int kFmt, class Epi>
 static int launch_conv(const ConvArgs& a, const Epi& epi, cudaStream_t stream) {
-    using S = GemmSmem<BLOCK_N>;
+    using S = GemmSmemFor<BLOCK_N, Epi>;
     const int c_blocks = ceil_div(a.C, kBlockK);
     const int cpad = c_blocks * kBlockK;
     CUtensorMap ta, tb;
@@ -21,22 +21,19 @@ static int launch_conv(const ConvArgs& a, const Epi& epi, cudaStream_t stream) {
         uint32_t box[4] = {64, (uint32_t)a.Fh, (uint32_t)(kBlockM / a.Fh), 1};
         Q3A_TRY(make_tmap_16bit(&ta, a.planes, 4, dims, strides, box));
     }
-    Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)(9 * cpad), (uint64_t)(9 * cpad), BLOCK_N));
+    Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)(9 * cpad), (uint64_t)(9 * cpad), BLOCK_N / 2));
     auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderConv, Epi>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        Q3A_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        attr_set = true;
-    }
+    int pairs = 0;
+    Q3A_TRY(gemm_prepare(kern, S::kTotal, &pairs));
     LoaderConv loader;
     loader.num_k_blocks = 9 * c_blocks;
     loader.c_blocks = c_blocks;
     loader.rows_per_tile = kBlockM / a.Fh;
     loader.last_block_steps = ceil_div(a.C - (c_blocks - 1) * kBlockK, kUmmaK);
     const int M = a.R_used * a.Fh;
-    const int tiles = ceil_div(M, kBlockM) * ceil_div(a.N, BLOCK_N);
-    const int grid = tiles < sm_count() ? tiles : sm_count();
-    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, M, a.N, loader, epi);
+    const int tiles = ceil_div(M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
+    const int grid = 2 * (tiles < pairs ? tiles : pairs);
+    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, ta /*unused: direct epilogue*/, M, a.N, loader, epi);
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;

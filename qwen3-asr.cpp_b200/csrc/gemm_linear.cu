@@ -4,6 +4,9 @@
 #include "epilogues.cuh"
 #include "tmap.h"
 
+#include <map>
+#include <mutex>
+
 namespace q3a {
 
 int sm_count() {
@@ -16,6 +19,35 @@ int sm_count() {
     return n;
 }
 
+int gemm_prepare_impl(const void* kernel, int smem_bytes, int threads, int* max_pairs) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, int> cache;
+    int dev = 0;
+    Q3A_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = cache.find({kernel, dev});
+    if (it != cache.end()) { *max_pairs = it->second; return Q3A_OK; }
+    Q3A_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * sm_count());
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = (size_t)smem_bytes;
+    cudaLaunchAttribute at;
+    at.id = cudaLaunchAttributeClusterDimension;
+    at.val.clusterDim.x = 2; at.val.clusterDim.y = 1; at.val.clusterDim.z = 1;
+    cfg.attrs = &at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        n = sm_count() / 2;
+    }
+    if (n > sm_count() / 2) n = sm_count() / 2;
+    cache[{kernel, dev}] = n;
+    *max_pairs = n;
+    return Q3A_OK;
+}
+
 int pick_block_n(int N) {
     if (N % 256 == 0) return 256;
     if (N % 224 == 0) return 224;
@@ -26,20 +58,18 @@ int pick_block_n(int N) {
 
 template <int BLOCK_N, int kFmt, class Epi>
 static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t stream) {
-    using S = GemmSmem<BLOCK_N>;
-    CUtensorMap ta, tb;
+    using S = GemmSmemFor<BLOCK_N, Epi>;
+    CUtensorMap ta, tb, tc_;
     Q3A_TRY(make_tmap_2d(&ta, a.a, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, kBlockM));
-    Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldw, BLOCK_N));
+    Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldw, BLOCK_N / 2));
+    Q3A_TRY(make_tmap_tile32(&tc_, a.out, Epi::kOutBytes, (uint64_t)a.M, (uint64_t)a.N, (uint64_t)a.ldc));
     auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderLinear, Epi>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        Q3A_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
-        attr_set = true;
-    }
+    int pairs = 0;
+    Q3A_TRY(gemm_prepare(kern, S::kTotal, &pairs));
     LoaderLinear loader{ceil_div(a.K, kBlockK)};
-    const int tiles = ceil_div(a.M, kBlockM) * ceil_div(a.N, BLOCK_N);
-    const int grid = tiles < sm_count() ? tiles : sm_count();
-    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, a.M, a.N, loader, epi);
+    const int tiles = ceil_div(a.M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
+    const int grid = 2 * (tiles < pairs ? tiles : pairs);
+    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, tc_, a.M, a.N, loader, epi);
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;
@@ -50,15 +80,16 @@ static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) 
     using OpT = typename std::conditional<kFmt == 1, __nv_bfloat16, __half>::type;
     switch (kind) {
         case EPI_BIAS_OP:
-            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, false>{(OpT*)a.out, a.ldc, a.bias}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, false>{a.bias}, stream);
         case EPI_BIAS_GELU_OP:
-            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, true>{(OpT*)a.out, a.ldc, a.bias}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, true>{a.bias}, stream);
         case EPI_BIAS_F32:
-            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<false>{(float*)a.out, a.ldc, a.bias, nullptr}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<false>{a.bias}, stream);
         case EPI_BIAS_RES_F32:
-            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<true>{(float*)a.out, a.ldc, a.bias, a.res}, stream);
+            if (a.res != a.out) { set_error("gemm_linear: the residual must be the output matrix (updated in place)"); return Q3A_ERR_ARG; }
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias}, stream);
         case EPI_POSEMB_F32:
-            return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32{(float*)a.out, a.ldc, a.pe, a.pos}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32{a.pe, a.pos, a.ldc, a.M}, stream);
     }
     set_error("gemm_linear: unknown epilogue");
     return Q3A_ERR_ARG;
@@ -77,7 +108,7 @@ static int dispatch_bn(EpiKind kind, const LinearArgs& a, int bn, cudaStream_t s
 
 int gemm_linear(EpiKind kind, int fmt, const LinearArgs& a, cudaStream_t stream) {
     if (a.M <= 0) return Q3A_OK;
-    if (a.K % 8 || a.N % 8 || a.lda % 8 || a.ldw % 8 || a.K <= 0 || a.N <= 0) {
+    if (a.K % 8 || a.N % 8 || a.lda % 8 || a.ldw % 8 || a.ldc % 8 || a.K <= 0 || a.N <= 0) {
         set_error("gemm_linear: K, N and leading dimensions must be positive multiples of 8");
         return Q3A_ERR_ARG;
     }

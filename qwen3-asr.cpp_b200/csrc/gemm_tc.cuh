@@ -1,48 +1,69 @@
-// Persistent warp-specialised tcgen05 GEMM for sm_100a:  D[M,N] = A[M,K] * W[N,K]^T, fp32 accumulate.
+// Persistent warp-specialised tcgen05 GEMM for sm_100a on CTA pairs:  D[M,N] = A[M,K] * W[N,K]^T, fp32 accumulate.
 //
-//   warp 0      : TMA producer (one lane) - A and W tiles into a kStages-deep smem ring
-//   warp 1      : MMA issuer  (one lane) - tcgen05.mma, accumulators in TMEM (2 buffers of 256 columns)
-//   warp 2      : TMEM allocator / deallocator
-//   warp 3      : idle
-//   warps 4..7  : epilogue - tcgen05.ld (one accumulator row per thread), fused functor, global store
+// Two CTAs on the two SMs of a TPC (cluster of 2) compute one 256 x BLOCK_N tile with
+// tcgen05.mma.cta_group::2: each CTA stages its own 128 rows of A and its own BLOCK_N/2 rows of W, the
+// tensor cores of both SMs read both halves, so every byte that crosses L2 -> SM feeds twice the math
+// of a single-CTA 128 x BLOCK_N tile (the single-CTA version of this kernel measured L2-bound at
+// ~44 B/clk/SM, profiles/r1a_*).  Accumulators: 128 lanes x BLOCK_N fp32 columns of TMEM per CTA,
+// two buffers, so the epilogue of tile i overlaps the MMAs of tile i+1.
 //
-// Both operands are K-major 16-bit (bf16 or f16) staged with 128-byte swizzle; a tile is
-// 128 x BLOCK_N with K blocks of 64.  The A-side coordinates come from a "loader" policy so the
-// same kernel runs the Linear layers (2-D tensor map) and the stride-2 3x3 convolutions of the
-// stem as implicit GEMM (4-D tensor map over parity-split channels-last planes, see stem.cuh).
+//   warp 0       TMA producer (one lane, both CTAs): A/W tiles into a kStages-deep smem ring; completion
+//                bytes of both CTAs are signalled on the leader CTA's "full" barrier
+//   warp 1       MMA issuer (one lane, leader CTA only); tcgen05.commit multicasts "slot free" and
+//                "accumulator ready" to both CTAs
+//   warp 2       TMEM allocator / deallocator (both CTAs, cta_group::2)
+//   warp 3       idle
+//   warps 4..11  epilogue, two warps per TMEM lane quadrant, alternating 32-column chunks:
+//                tcgen05.ld -> fused functor -> swizzled smem staging -> TMA store (coalesced, async);
+//                the residual stream is brought in by TMA loads one chunk ahead.  The convolution
+//                epilogues scatter rows and store straight from registers instead.
+//
+// Both operands are K-major 16-bit (bf16 or f16) staged with 128-byte swizzle, K blocks of 64.  The A-side
+// coordinates come from a "loader" policy so the same kernel runs the Linear layers (2-D tensor map) and
+// the stride-2 3x3 convolutions of the stem as implicit GEMM (4-D tensor map over parity-split
+// channels-last planes, see stem.h).
 #pragma once
 #include "common.cuh"
 #include "tc.cuh"
 
 namespace q3a {
 
-constexpr int kBlockM = 128;
+constexpr int kBlockM = 128;                // rows per CTA; a pair covers 256
 constexpr int kBlockK = 64;                 // 64 x 16-bit = 128 B = one swizzle span
 constexpr int kUmmaK = 16;
-constexpr int kGemmThreads = 256;
+constexpr int kGemmThreads = 384;           // 4 control warps + 8 epilogue warps
+constexpr int kEpiWarps = 8;
 constexpr int kTmemCols = 512;              // two accumulator buffers of up to 256 columns
+constexpr int kSmemLimit = 232448;          // 227 KB opt-in maximum per CTA
 
-template <int BLOCK_N> struct GemmSmem {
-    static constexpr int kABytes = kBlockM * kBlockK * 2;          // 16 KB
-    static constexpr int kBBytes = BLOCK_N * kBlockK * 2;
+// kEpiBufBytes: bytes of one epilogue staging buffer (32 rows), kEpiBufs: buffers per epilogue warp
+template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs> struct GemmSmem {
+    static constexpr int kABytes = kBlockM * kBlockK * 2;              // 16 KB
+    static constexpr int kBBytes = (BLOCK_N / 2) * kBlockK * 2;        // this CTA's half of the W tile
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (200 * 1024) / kStageBytes > 6 ? 6 : (200 * 1024) / kStageBytes;
-    static constexpr int kBarrierBytes = 256;
-    static constexpr int kTotal = kStages * kStageBytes + kBarrierBytes + 1024;   // +1024: manual alignment
+    static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;
+    static constexpr int kBarrierBytes = 512;
+    static constexpr int kAvail = kSmemLimit - 1024 - kBarrierBytes - kEpiBytes;
+    static constexpr int kStages = kAvail / kStageBytes > 6 ? 6 : kAvail / kStageBytes;
+    static constexpr int kTotal = kStages * kStageBytes + kEpiBytes + kBarrierBytes + 1024;   // +1024: manual alignment
     static_assert(kStageBytes % 1024 == 0, "stage must keep 1024-B swizzle alignment");
-    static_assert(kStages >= 2, "need at least double buffering");
+    static_assert(kStages >= 3, "need at least three stages");
 };
+// the shared-memory plan of a (BLOCK_N, epilogue) instantiation, for kernel and host alike
+template <int BLOCK_N, class Epi>
+using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes : 0,
+                             Epi::kStaged ? (Epi::kResidual ? 3 : 2) : 0>;
 
-// ---- A-operand coordinate policies --------------------------------------------------------
+// ---- A-operand coordinate policies (m128 = index of this CTA's 128-row block) -----------------
 // Linear: A is [M][K] row-major, tensor map dims {K, M}, box {64, 128}.
 struct LoaderLinear {
     int num_k_blocks;
-    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m_blk, int kb) const {
-        tc::tma_load_2d(dst, tmap, bar, kb * kBlockK, m_blk * kBlockM);
+    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m128, int kb) const {
+        tc::tma_load_2d_pair(dst, tmap, bar, kb * kBlockK, m128 * kBlockM);
     }
     __device__ __forceinline__ int k_steps(int) const { return kBlockK / kUmmaK; }
 };
-// Conv (3x3, stride 2, pad 1) over parity-split planes (layout in stem.cuh): tensor map dims
+// Conv (3x3, stride 2, pad 1) over parity-split planes (layout in stem.h): tensor map dims
 // {C, Fh, R, 4 planes}, box {64, Fh, 128/Fh, 1}.  Output row m = R_out * Fh + of where R_out indexes
 // (chunk, 1 + ot).  K index = tap * (c_blocks*64) + c, tap = dt*3 + df (dt: time tap, df: mel tap).
 //   dt=0 -> odd-time plane, row R_out-1 ; dt=1 -> even-time plane, row R_out ; dt=2 -> odd-time plane, row R_out
@@ -54,148 +75,266 @@ struct LoaderConv {
     int c_blocks;           // ceil(C / 64)
     int rows_per_tile;      // 128 / Fh
     int last_block_steps;   // k-steps that hold real channels in the last channel block of a tap
-    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m_blk, int kb) const {
+    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m128, int kb) const {
         const int tap = kb / c_blocks, cb = kb - tap * c_blocks;
         const int dt = tap / 3, df = tap - dt * 3;
         const int plane = ((dt != 1) ? 2 : 0) + ((df != 1) ? 1 : 0);
-        tc::tma_load_4d(dst, tmap, bar, cb * kBlockK, (df == 0) ? -1 : 0,
-                        m_blk * rows_per_tile + ((dt == 0) ? -1 : 0), plane);
+        tc::tma_load_4d_pair(dst, tmap, bar, cb * kBlockK, (df == 0) ? -1 : 0,
+                             m128 * rows_per_tile + ((dt == 0) ? -1 : 0), plane);
     }
     __device__ __forceinline__ int k_steps(int kb) const {
         return ((kb % c_blocks) == c_blocks - 1) ? last_block_steps : kBlockK / kUmmaK;
     }
 };
 
+// byte offset of 16-byte chunk j of row r inside a 32-row staging buffer whose rows are kRowBytes long,
+// in the layout TMA expects for SWIZZLE_128B (128-B rows) / SWIZZLE_64B (64-B rows)
+template <int kRowBytes>
+__device__ __forceinline__ uint32_t stage_off(int r, int j) {
+    if (kRowBytes == 128) return (uint32_t)(r * 128 + ((j ^ (r & 7)) << 4));
+    return (uint32_t)(r * 64 + ((j ^ ((r >> 1) & 3)) << 4));
+}
+
 // ---- the kernel ------------------------------------------------------------------------------
-// Epilogue contract:  struct E { __device__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const; }
-// is called once per (row m < M, 32-column group starting at n0 < N); only the first `nvalid`
-// (a multiple of 8, <= 32) columns of the group belong to the output.
+// Epilogue contracts (epilogues.cuh):
+//   staged   struct E { static constexpr bool kStaged = true; using OutT = float | bf16 | f16;
+//                       static constexpr bool kResidual;      // out += previous contents of out (f32 only)
+//                       __device__ void apply(int m, int n0, int nvalid, float (&v)[32]) const; }
+//            v holds the accumulators of row m, columns n0..n0+31 on entry and the values to store on
+//            exit (the kernel adds the residual afterwards); tmap_c describes the output matrix.
+//   direct   struct E { static constexpr bool kStaged = false;
+//                       __device__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const; }
+//            called for rows m < M; only the first nvalid (multiple of 8) columns belong to the output.
 template <int BLOCK_N, int kFmt, class Loader, class Epilogue>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               int M, int N, Loader loader, Epilogue epi) {
-    using S = GemmSmem<BLOCK_N>;
+               const __grid_constant__ CUtensorMap tmap_c, int M, int N, Loader loader, Epilogue epi) {
+    constexpr bool kStaged = Epilogue::kStaged;
+    constexpr bool kResidual = Epilogue::kResidual;
+    constexpr int kOutBytes = Epilogue::kOutBytes;                     // 4 or 2 (staged only)
+    constexpr int kRowBytes = 32 * kOutBytes;                          // staging row: 32 columns
+    constexpr int kBufBytes = kStaged ? 32 * kRowBytes : 0;
+    constexpr int kEpiBufs = kStaged ? (kResidual ? 3 : 2) : 0;
+    using S = GemmSmemFor<BLOCK_N, Epilogue>;
     constexpr int kStages = S::kStages;
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "BLOCK_N must be a multiple of 16, at most 256");
+    static_assert(!kStaged || BLOCK_N % 32 == 0, "staged epilogues store whole 32-column chunks");
+    static_assert(!kResidual || kOutBytes == 4, "the residual stream is fp32");
 
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + kStages * S::kStageBytes;
+    uint8_t* smem_gen = smem_raw + (smem_base - tc::smem_u32(smem_raw));
+    const uint32_t epi_base = smem_base + kStages * S::kStageBytes;
+    const uint32_t bar_base = epi_base + S::kEpiBytes;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
     auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * kStages + s); };
     auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
-    uint8_t* smem_gen = smem_raw + (smem_base - tc::smem_u32(smem_raw));
-    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes +
-                                                                            8 * (2 * kStages + 4));
+    auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * kStages + 5 + w * 3 + b); };   // 24 barriers
+    static_assert(8 * (2 * 6 + 5 + 24) <= S::kBarrierBytes, "barrier block too small");
+    volatile uint32_t* tmem_slot_ptr =
+        reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + S::kEpiBytes + 8 * (2 * kStages + 4));
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int m_blocks = ceil_div(M, kBlockM), n_blocks = ceil_div(N, BLOCK_N);
+    const uint32_t rank = tc::cluster_ctarank();                       // 0 = leader (issues the MMAs)
+    const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+    const int m_blocks = ceil_div(M, 2 * kBlockM), n_blocks = ceil_div(N, BLOCK_N);
     const int num_tiles = m_blocks * n_blocks;
     const int num_kb = loader.num_k_blocks;
 
     if (warp == 0 && lane == 0) {
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
+        if (kStaged) tc::prefetch_tmap(&tmap_c);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), 1); }
-        for (int s = 0; s < 2; ++s) { tc::mbar_init(tfull_bar(s), 1); tc::mbar_init(tempty_bar(s), 4); }
+        for (int s = 0; s < 2; ++s) { tc::mbar_init(tfull_bar(s), 1); tc::mbar_init(tempty_bar(s), 2 * kEpiWarps); }
+        for (int w = 0; w < kEpiWarps; ++w)
+            for (int b = 0; b < 3; ++b) tc::mbar_init(res_bar(w, b), 1);
         tc::fence_barrier_init();
     }
-    if (warp == 2) tc::tmem_alloc<kTmemCols>(tmem_slot);
+    if (warp == 2) tc::tmem_alloc_pair<kTmemCols>(tmem_slot);
     tc::fence_before_sync();
-    __syncthreads();
+    tc::cluster_sync();                       // barriers of both CTAs initialised before any remote signal
     tc::fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
+        // ===================== TMA producer (both CTAs) =====================
         if (lane == 0) {
             uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                // n fastest: CTAs running side by side share the A tile through L2
+            for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+                // n fastest: pairs running side by side share the A tile through L2
                 const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
+                const int m128 = 2 * m_blk + (int)rank;
                 for (int kb = 0; kb < num_kb; ++kb, ++it) {
                     const int s = it % kStages;
                     const uint32_t ph = (it / kStages) & 1;
                     tc::mbar_wait(empty_bar(s), ph ^ 1);
                     const uint32_t a_dst = smem_base + s * S::kStageBytes;
                     const uint32_t b_dst = a_dst + S::kABytes;
-                    tc::mbar_arrive_expect_tx(full_bar(s), S::kStageBytes);
-                    loader.load_a(a_dst, &tmap_a, full_bar(s), m_blk, kb);
-                    tc::tma_load_2d(b_dst, &tmap_b, full_bar(s), kb * kBlockK, n_blk * BLOCK_N);
+                    if (rank == 0) tc::mbar_arrive_expect_tx(full_bar(s), 2 * S::kStageBytes);
+                    const uint32_t bar = tc::mapa(full_bar(s), 0);
+                    loader.load_a(a_dst, &tmap_a, bar, m128, kb);
+                    tc::tma_load_2d_pair(b_dst, &tmap_b, bar, kb * kBlockK, n_blk * BLOCK_N + (int)rank * (BLOCK_N / 2));
                 }
             }
         }
+        __syncwarp();
     } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        constexpr uint32_t idesc = tc::make_idesc(kFmt, kBlockM, BLOCK_N, 0, 0);
-        uint32_t it = 0, local = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
-            const int as = local & 1;
-            const uint32_t aph = (local >> 1) & 1;
-            tc::mbar_wait(tempty_bar(as), aph ^ 1);
-            tc::fence_after_sync();
-            const uint32_t d_tmem = tmem_base + as * 256;
-            for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                const int s = it % kStages;
-                const uint32_t ph = (it / kStages) & 1;
-                tc::mbar_wait(full_bar(s), ph);
+        // ===================== MMA issuer (leader CTA) =====================
+        if (rank == 0) {
+            constexpr uint32_t idesc = tc::make_idesc(kFmt, 2 * kBlockM, BLOCK_N, 0, 0);
+            uint32_t it = 0, local = 0;
+            for (int tile = pair; tile < num_tiles; tile += num_pairs, ++local) {
+                const int as = local & 1;
+                const uint32_t aph = (local >> 1) & 1;
+                tc::mbar_wait(tempty_bar(as), aph ^ 1);
                 tc::fence_after_sync();
-                if (lane == 0) {
-                    const uint32_t a_addr = smem_base + s * S::kStageBytes;
-                    const uint32_t b_addr = a_addr + S::kABytes;
-                    const uint64_t a_desc = tc::smem_desc_kmajor_sw128(a_addr);
-                    const uint64_t b_desc = tc::smem_desc_kmajor_sw128(b_addr);
-                    const int steps = loader.k_steps(kb);
+                const uint32_t d_tmem = tmem_base + as * 256;
+                for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                    const int s = it % kStages;
+                    const uint32_t ph = (it / kStages) & 1;
+                    tc::mbar_wait(full_bar(s), ph);
+                    tc::fence_after_sync();
+                    if (lane == 0) {
+                        const uint32_t a_addr = smem_base + s * S::kStageBytes;
+                        const uint32_t b_addr = a_addr + S::kABytes;
+                        const uint64_t a_desc = tc::smem_desc_kmajor_sw128(a_addr);
+                        const uint64_t b_desc = tc::smem_desc_kmajor_sw128(b_addr);
+                        const int steps = loader.k_steps(kb);
 #pragma unroll
-                    for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-                        // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
-                        if (k < steps) tc::mma_f16_ss(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
+                            if (k < steps)
+                                tc::mma_f16_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                        }
+                        tc::mma_commit_pair(empty_bar(s), 3);                        // frees the slot in both CTAs
+                        if (kb == num_kb - 1) tc::mma_commit_pair(tfull_bar(as), 3);   // accumulators complete
                     }
-                    tc::mma_commit(empty_bar(s));                      // frees the smem slot when the MMAs retire
-                    if (kb == num_kb - 1) tc::mma_commit(tfull_bar(as));   // accumulator complete
+                    __syncwarp();
                 }
-                __syncwarp();
             }
         }
     } else if (warp >= 4) {
-        // ===================== epilogue =====================
+        // ===================== epilogue (both CTAs) =====================
+        const int ew = warp - 4;
         const int q = warp & 3;                       // TMEM lane quadrant this warp may read
+        const int hf = ew >> 2;                       // which half of the 32-column chunks
+        const uint32_t tempty_leader0 = tc::mapa(tempty_bar(0), 0), tempty_leader1 = tc::mapa(tempty_bar(1), 0);
+        const uint32_t my_bufs = epi_base + ew * kEpiBufs * kBufBytes;
+        uint8_t* my_bufs_gen = smem_gen + kStages * S::kStageBytes + ew * kEpiBufs * kBufBytes;
+        uint32_t seq = 0;                             // chunks processed by this warp (staging buffer rotation)
+        uint32_t rph = 0;                             // phase bits of the residual barriers
         uint32_t local = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++local) {
+
+        auto chunks_of = [&](int n_blk) { return ceil_div(min(BLOCK_N, N - n_blk * BLOCK_N), 32); };
+        // residual prefetch for the chunk with sequence number sq at (tile, chunk c)
+        auto issue_res = [&](uint32_t sq, int tile, int c) {
+            const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
+            const int b = sq % 3;
+            tc::mbar_arrive_expect_tx(res_bar(ew, b), kBufBytes);
+            tc::tma_load_2d(my_bufs + b * kBufBytes, &tmap_c, res_bar(ew, b), n_blk * BLOCK_N + c * 32,
+                            (2 * m_blk + (int)rank) * kBlockM + q * 32);
+        };
+        // first tile at or after t (in this pair's sequence) in which this warp owns a chunk
+        auto tile_with_chunk = [&](int t) {
+            while (t < num_tiles && hf >= chunks_of(t % n_blocks)) t += num_pairs;
+            return t;
+        };
+        if (kResidual && lane == 0) {
+            const int t0 = tile_with_chunk(pair);
+            if (t0 < num_tiles) issue_res(0, t0, hf);
+        }
+
+        for (int tile = pair; tile < num_tiles; tile += num_pairs, ++local) {
             const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
             const int as = local & 1;
             const uint32_t aph = (local >> 1) & 1;
+            const int nch = chunks_of(n_blk);
             tc::mbar_wait(tfull_bar(as), aph);
             tc::fence_after_sync();
-            const int m = m_blk * kBlockM + q * 32 + lane;
+            const int m0 = (2 * m_blk + (int)rank) * kBlockM + q * 32;
+            const int m = m0 + lane;
             const uint32_t t_row = tmem_base + as * 256 + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-            for (int c = 0; c < BLOCK_N; c += 32) {
+            for (int c = hf; c < nch; c += 2) {
+                const int n0 = n_blk * BLOCK_N + c * 32;
+                const int nvalid = min(32, min(BLOCK_N - c * 32, N - n0));
+                if (kResidual && lane == 0) {
+                    // next chunk of this warp: same tile, or the first chunk of its next tile
+                    int nt = tile, nc = c + 2;
+                    if (nc >= nch) { nt = tile_with_chunk(tile + num_pairs); nc = hf; }
+                    if (nt < num_tiles) {
+                        tc::bulk_wait_group_read<1>();          // the store that last used that buffer has read it
+                        issue_res(seq + 1, nt, nc);
+                    }
+                }
                 uint32_t r[32];
-                tc::tmem_ld_32x32b_x32(t_row + c, r);
+                tc::tmem_ld_32x32b_x32(t_row + c * 32, r);
                 tc::tmem_ld_wait();
-                const int n0 = n_blk * BLOCK_N + c;
-                if (m < M && n0 < N) {
-                    float acc[32];
+                float v[32];
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) acc[j] = __uint_as_float(r[j]);
-                    int nvalid = min(32, min(BLOCK_N - c, N - n0));
-                    epi(m, n0, nvalid, acc);
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                if constexpr (!kStaged) {
+                    if (m < M) epi(m, n0, nvalid, v);
+                } else {
+                    epi.apply(m, n0, nvalid, v);
+                    const int b = seq % kEpiBufs;
+                    uint8_t* buf = my_bufs_gen + b * kBufBytes;
+                    if constexpr (kResidual) {
+                        tc::mbar_wait(res_bar(ew, b), (rph >> b) & 1);
+                        rph ^= 1u << b;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            float4* p = reinterpret_cast<float4*>(buf + stage_off<128>(lane, j));
+                            float4 x = *p;
+                            x.x += v[4 * j + 0]; x.y += v[4 * j + 1]; x.z += v[4 * j + 2]; x.w += v[4 * j + 3];
+                            *p = x;
+                        }
+                    } else {
+                        if (lane == 0) tc::bulk_wait_group_read<kEpiBufs - 1>();   // buffer b's previous store has read it
+                        __syncwarp();
+                        if constexpr (kOutBytes == 4) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                *reinterpret_cast<float4*>(buf + stage_off<128>(lane, j)) =
+                                    make_float4(v[4 * j + 0], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                uint4 u;
+                                u.x = Epilogue::pack2(v[8 * j + 0], v[8 * j + 1]);
+                                u.y = Epilogue::pack2(v[8 * j + 2], v[8 * j + 3]);
+                                u.z = Epilogue::pack2(v[8 * j + 4], v[8 * j + 5]);
+                                u.w = Epilogue::pack2(v[8 * j + 6], v[8 * j + 7]);
+                                *reinterpret_cast<uint4*>(buf + stage_off<64>(lane, j)) = u;
+                            }
+                        }
+                    }
+                    tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the TMA store
+                    __syncwarp();
+                    if (lane == 0) {
+                        tc::tma_store_2d(&tmap_c, my_bufs + b * kBufBytes, n0, m0);
+                        tc::bulk_commit_group();
+                    }
+                    ++seq;
                 }
             }
+            // every tcgen05.ld of this tile has completed: hand the accumulator buffer back to the MMA issuer
             tc::fence_before_sync();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(tempty_bar(as));
+            if (lane == 0) tc::mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
         }
+        if (kStaged && lane == 0) tc::bulk_wait_group<0>();
     }
 
+    __syncwarp();
     tc::fence_before_sync();
-    __syncthreads();
-    if (warp == 2) tc::tmem_dealloc<kTmemCols>(tmem_base);
+    tc::cluster_sync();                       // nobody leaves while the pair's MMAs / remote signals are in flight
+    if (warp == 2) tc::tmem_dealloc_pair<kTmemCols>(tmem_base);
 }
 
 }  // namespace q3a

@@ -44,6 +44,26 @@ int make_tmap_16bit(CUtensorMap* out, const void* base, int rank, const uint64_t
     return Q3A_OK;
 }
 
+int make_tmap_tile32(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld) {
+    std::call_once(g_once, resolve);
+    if (!g_encode) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return Q3A_ERR_CUDA; }
+    if (elem_bytes != 2 && elem_bytes != 4) { set_error("make_tmap_tile32: element size must be 2 or 4"); return Q3A_ERR_ARG; }
+    cuuint64_t d[2] = {cols, rows};
+    cuuint64_t s[1] = {ld * (uint64_t)elem_bytes};
+    cuuint32_t b[2] = {32, 32};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = g_encode(out, elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                          const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          elem_bytes == 4 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (32x32 tile map) failed with code " + std::to_string((int)r) + " rows " +
+                  std::to_string(rows) + " cols " + std::to_string(cols) + " ld " + std::to_string(ld));
+        return Q3A_ERR_CUDA;
+    }
+    return Q3A_OK;
+}
+
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
     uint64_t dims[2] = {cols, rows};
     uint64_t strides[1] = {ld * 2};

@@ -15,4 +15,8 @@ int make_tmap_16bit(CUtensorMap* out, const void* base, int rank, const uint64_t
 // row-major [rows][cols] 16-bit matrix with leading dimension ld (elements); box = {64, box_rows}
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows);
 
+// row-major [rows][cols] matrix of 2- or 4-byte elements, box = 32 x 32 elements, swizzle = the box's row
+// bytes (64 B for 16-bit, 128 B for f32): the GEMM epilogue's staged stores and residual loads
+int make_tmap_tile32(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld);
+
 }  // namespace q3a
