@@ -6,12 +6,19 @@
 // utterance for the ASR encoder (no mask), 104-token windows for the aligner.  Scores are never
 // written to HBM.
 //
-// One CTA = one (128-query tile, head).  Per 128-key block:
-//   S[128 x nk] = Q K^T        tcgen05.mma, operands K-major in smem (TMA, 128B swizzle), S in TMEM
-//   online softmax             one query row per thread (tcgen05.ld), exp2 with folded scale, fp32
-//   P -> smem (16-bit, swizzled K-major), O_blk[128 x 64] = P V   tcgen05.mma, V is the MN-major B operand
-//   O = alpha * O + O_blk      fp32 registers
-// K/V blocks are double-buffered so the next TMA overlaps the current block's math.
+// One CTA (128 threads, one query row per thread, two CTAs per SM) = one (128-query tile, head).
+// Per 128-key block j:
+//   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,128); issued one block ahead, so it runs
+//                            while the threads are still busy with block j-1
+//   S_j -> registers         four tcgen05.ld.x32 back to back, one wait
+//   softmax                  row maximum, p = exp2(s*scale - m) with a lazily updated reference maximum m
+//                            (O in TMEM is rescaled only when the row maximum grows by more than 2^8, so the
+//                            common block never reads O back), row sum in fp32
+//   P_j -> smem (16-bit, 128-byte swizzled K-major), O += P_j V_j   tcgen05.mma accumulating in TMEM
+//                            columns [128,192); V is the MN-major B operand
+// K and V blocks are double-buffered with separate barriers: K_{j+2} is fetched as soon as Q K_j^T has
+// retired, V_{j+1} as soon as P_{j-1} V_{j-1} has.  Warps whose 32 query rows all lie past the end of the
+// segment skip the softmax arithmetic.  The epilogue divides by the row sum and stores 16-bit rows.
 #include "attention.h"
 #include "tc.cuh"
 #include "tmap.h"
@@ -22,26 +29,28 @@ constexpr int kHd = 64;
 constexpr int kQT = 128;                 // queries per CTA
 constexpr int kKT = 128;                 // keys per block
 constexpr int kTileBytes = 128 * 64 * 2; // 16 KB: [128 rows][64 x 16-bit]
-constexpr int kAttnSmem = 1024 /*align*/ + kTileBytes /*Q*/ + 4 * kTileBytes /*K,V x2*/ + 2 * kTileBytes /*P*/ + 128;
-constexpr int kAttnTmemCols = 256;       // S: columns [0,128), O_blk: columns [128,192)
+constexpr int kAttnSmem = kTileBytes /*Q*/ + 4 * kTileBytes /*K,V x2*/ + 2 * kTileBytes /*P*/ + 128;
+constexpr int kAttnTmemCols = 256;       // S: columns [0,128), O: columns [128,192)
+constexpr float kRescaleThreshold = 8.0f;   // log2 units: p <= 2^8 between rescales
 
 template <class OpT>
 __global__ void __launch_bounds__(128, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* __restrict__ tiles,
                  OpT* __restrict__ out, int d_model) {
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
-    uint8_t* gen = smem_raw + (base - tc::smem_u32(smem_raw));
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    const uint32_t base = tc::smem_u32(smem_raw);
+    if (base & 1023u) { asm volatile("trap;"); }          // the swizzled tiles need 1024-byte alignment
     const uint32_t sQ = base;
-    auto sK = [&](int b) { return base + kTileBytes * (1 + 2 * b); };
-    auto sV = [&](int b) { return base + kTileBytes * (2 + 2 * b); };
+    auto sK = [&](int b) { return base + kTileBytes * (1 + b); };
+    auto sV = [&](int b) { return base + kTileBytes * (3 + b); };
     const uint32_t sP = base + 5 * kTileBytes;
-    uint8_t* gP = gen + 5 * kTileBytes;
+    uint8_t* gP = smem_raw + 5 * kTileBytes;
     const uint32_t bars = base + 7 * kTileBytes;
     const uint32_t bar_q = bars, bar_s = bars + 8, bar_o = bars + 16;
-    auto bar_kv = [&](int b) { return bars + 24 + 8 * b; };
-    const uint32_t tmem_slot = bars + 48;
-    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(gen + 7 * kTileBytes + 48);
+    auto bar_k = [&](int b) { return bars + 24 + 8 * b; };
+    auto bar_v = [&](int b) { return bars + 40 + 8 * b; };
+    const uint32_t tmem_slot = bars + 56;
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + 7 * kTileBytes + 56);
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const AttnTile t = tiles[blockIdx.x];
@@ -49,11 +58,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
     const int seg_len = t.seg_end - t.seg_start;
     const int nkv = (seg_len + kKT - 1) / kKT;
     const int col_q = head * kHd, col_k = d_model + head * kHd, col_v = 2 * d_model + head * kHd;
+    constexpr int kFmt = OpTraits<OpT>::kFmt;
 
     if (tid == 0) {
         tc::prefetch_tmap(&tmap_qkv);
         tc::mbar_init(bar_q, 1); tc::mbar_init(bar_s, 1); tc::mbar_init(bar_o, 1);
-        tc::mbar_init(bar_kv(0), 1); tc::mbar_init(bar_kv(1), 1);
+        tc::mbar_init(bar_k(0), 1); tc::mbar_init(bar_k(1), 1);
+        tc::mbar_init(bar_v(0), 1); tc::mbar_init(bar_v(1), 1);
         tc::fence_barrier_init();
     }
     if (warp == 0) tc::tmem_alloc<kAttnTmemCols>(tmem_slot);
@@ -63,125 +74,191 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
     const uint32_t tmem = *tmem_slot_ptr;
     const uint32_t t_row = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane quadrant
 
+    auto keys_of = [&](int j) {                                      // keys block j feeds to the MMAs
+        const int rem = seg_len - j * kKT;
+        return rem >= kKT ? kKT : ((rem + 15) & ~15);
+    };
+    auto issue_qk = [&](int j) {                                     // tid 0 only
+        tc::mbar_wait(bar_k(j & 1), (j >> 1) & 1);
+        tc::fence_after_sync();
+        const uint32_t idesc = tc::make_idesc(kFmt, kQT, keys_of(j), 0, 0);
+        const uint64_t a = tc::smem_desc_kmajor_sw128(sQ), b = tc::smem_desc_kmajor_sw128(sK(j & 1));
+#pragma unroll
+        for (int k = 0; k < kHd / 16; ++k) tc::mma_f16_ss(tmem, a + 2 * k, b + 2 * k, idesc, k != 0);
+        tc::mma_commit(bar_s);
+    };
+
     if (tid == 0) {
         tc::mbar_arrive_expect_tx(bar_q, kTileBytes);
         tc::tma_load_2d(sQ, &tmap_qkv, bar_q, col_q, t.q0);
-        tc::mbar_arrive_expect_tx(bar_kv(0), 2 * kTileBytes);
-        tc::tma_load_2d(sK(0), &tmap_qkv, bar_kv(0), col_k, t.seg_start);
-        tc::tma_load_2d(sV(0), &tmap_qkv, bar_kv(0), col_v, t.seg_start);
+        tc::mbar_arrive_expect_tx(bar_k(0), kTileBytes);
+        tc::tma_load_2d(sK(0), &tmap_qkv, bar_k(0), col_k, t.seg_start);
+        tc::mbar_arrive_expect_tx(bar_v(0), kTileBytes);
+        tc::tma_load_2d(sV(0), &tmap_qkv, bar_v(0), col_v, t.seg_start);
+        if (nkv > 1) {
+            tc::mbar_arrive_expect_tx(bar_k(1), kTileBytes);
+            tc::tma_load_2d(sK(1), &tmap_qkv, bar_k(1), col_k, t.seg_start + kKT);
+        }
+        tc::mbar_wait(bar_q, 0);
+        issue_qk(0);
     }
 
-    constexpr int kFmt = OpTraits<OpT>::kFmt;
     const float kScale = 0.125f * 1.4426950408889634f;   // 1/sqrt(64) * log2(e)
-    float m_run = -INFINITY, l_run = 0.0f;
-    float o[kHd];
-#pragma unroll
-    for (int i = 0; i < kHd; ++i) o[i] = 0.0f;
+    const bool row_live = (t.q0 + warp * 32) < t.seg_end;  // warp-uniform: any valid query row in this warp
+    float m_ref = 0.0f, l_run = 0.0f;
 
     for (int j = 0; j < nkv; ++j) {
-        const int buf = j & 1;
         const int rem = seg_len - j * kKT;
-        const int nk = rem >= kKT ? kKT : ((rem + 15) & ~15);      // keys this block feeds to the MMAs
-        if (tid == 0) {
-            if (j + 1 < nkv) {                                      // prefetch the next block
-                const int nb = buf ^ 1;
-                tc::mbar_arrive_expect_tx(bar_kv(nb), 2 * kTileBytes);
-                tc::tma_load_2d(sK(nb), &tmap_qkv, bar_kv(nb), col_k, t.seg_start + (j + 1) * kKT);
-                tc::tma_load_2d(sV(nb), &tmap_qkv, bar_kv(nb), col_v, t.seg_start + (j + 1) * kKT);
-            }
-            if (j == 0) tc::mbar_wait(bar_q, 0);
-            tc::mbar_wait(bar_kv(buf), (j >> 1) & 1);
-            tc::fence_after_sync();
-            const uint32_t idesc = tc::make_idesc(kFmt, kQT, nk, 0, 0);
-            const uint64_t a = tc::smem_desc_kmajor_sw128(sQ), b = tc::smem_desc_kmajor_sw128(sK(buf));
-#pragma unroll
-            for (int k = 0; k < kHd / 16; ++k) tc::mma_f16_ss(tmem, a + 2 * k, b + 2 * k, idesc, k != 0);
-            tc::mma_commit(bar_s);
-        }
+        const int nk = keys_of(j);
+        const int n_valid = rem < kKT ? rem : kKT;
+        // ---- S_j -> registers ---------------------------------------------------------------------
         tc::mbar_wait(bar_s, j & 1);
         tc::fence_after_sync();
-
-        // ---- pass 1: row maximum over the block's valid keys ----------------------------------------
-        const int n_valid = rem < kKT ? rem : kKT;
-        float mx = -INFINITY;
-        for (int c = 0; c < nk; c += 32) {
-            uint32_t r[32];
-            tc::tmem_ld_32x32b_x32(t_row + c, r);
-            tc::tmem_ld_wait();
+        uint32_t s[128];
+        if (row_live) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-                if (c + i < n_valid) mx = fmaxf(mx, __uint_as_float(r[i]));
+            for (int c = 0; c < 4; ++c)
+                if (c * 32 < nk) tc::tmem_ld_32x32b_x32(t_row + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
+            tc::tmem_ld_wait();
         }
-        const float m_new = fmaxf(m_run, mx * kScale);
-        const float alpha = exp2f(m_run - m_new);
-        m_run = m_new;
-        // ---- pass 2: p = exp2(s*scale - m), row sum, P -> swizzled smem -----------------------------
+        tc::fence_before_sync();
+        __syncthreads();                                   // S is in registers everywhere: TMEM S and K_j are free
+        if (tid == 0) {
+            tc::fence_after_sync();
+            if (j + 2 < nkv) {
+                tc::mbar_arrive_expect_tx(bar_k(j & 1), kTileBytes);
+                tc::tma_load_2d(sK(j & 1), &tmap_qkv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
+            }
+            if (j + 1 < nkv) issue_qk(j + 1);
+        }
+        __syncwarp();
+        // ---- softmax on registers -------------------------------------------------------------------
         float psum = 0.0f;
-        for (int c = 0; c < nk; c += 32) {
-            uint32_t r[32];
-            tc::tmem_ld_32x32b_x32(t_row + c, r);
-            tc::tmem_ld_wait();
-            float p[32];
+        uint32_t pk[64];                                   // P row, packed 16-bit pairs
+        if (row_live) {
+            float mx = -INFINITY;
+            if (n_valid == kKT) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                p[i] = (c + i < n_valid) ? exp2f(fmaf(__uint_as_float(r[i]), kScale, -m_new)) : 0.0f;
-                psum += p[i];
+                for (int i = 0; i < 128; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+            } else {
+#pragma unroll
+                for (int i = 0; i < 128; ++i)
+                    if (i < nk && i < n_valid) mx = fmaxf(mx, __uint_as_float(s[i]));
             }
-            // 64-key sub-tile (c / 64), 16-byte chunks ((c % 64) / 8 + g), XOR-swizzled with row % 8
-            uint8_t* prow = gP + (c >> 6) * kTileBytes + tid * 128;
-            const int ch0 = (c & 63) >> 3;
+            mx *= kScale;
+            if (j == 0) {
+                m_ref = mx;
+            } else {
+                const bool grow = mx > m_ref + kRescaleThreshold;
+                if (__any_sync(0xffffffffu, grow)) {
+                    // rare: bring O (complete up to block j-1) and l to the new reference maximum
+                    const float alpha = grow ? tc::ex2_approx(m_ref - mx) : 1.0f;
+                    if (grow) m_ref = mx;
+                    l_run *= alpha;
+                    tc::mbar_wait(bar_o, (j - 1) & 1);
+                    tc::fence_after_sync();
 #pragma unroll
-            for (int g = 0; g < 4; ++g) {
-                uint4 u;
-                u.x = OpTraits<OpT>::pack2(p[g * 8 + 0], p[g * 8 + 1]);
-                u.y = OpTraits<OpT>::pack2(p[g * 8 + 2], p[g * 8 + 3]);
-                u.z = OpTraits<OpT>::pack2(p[g * 8 + 4], p[g * 8 + 5]);
-                u.w = OpTraits<OpT>::pack2(p[g * 8 + 6], p[g * 8 + 7]);
-                *reinterpret_cast<uint4*>(prow + (((ch0 + g) ^ (tid & 7)) << 4)) = u;
+                    for (int c = 0; c < kHd; c += 32) {
+                        uint32_t r[32];
+                        tc::tmem_ld_32x32b_x32(t_row + 128 + c, r);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
+                        tc::tmem_st_32x32b_x32(t_row + 128 + c, r);
+                    }
+                    tc::tmem_st_wait();
+                }
+            }
+            const float neg_m = -m_ref;
+            if (n_valid == kKT) {
+#pragma unroll
+                for (int i = 0; i < 128; i += 2) {
+                    const float p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i]), kScale, neg_m));
+                    const float p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + 1]), kScale, neg_m));
+                    psum += p0 + p1;
+                    pk[i >> 1] = OpTraits<OpT>::pack2(p0, p1);
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 128; i += 2) {
+                    float p0 = 0.0f, p1 = 0.0f;
+                    if (i < nk) {
+                        if (i < n_valid) p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i]), kScale, neg_m));
+                        if (i + 1 < n_valid) p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + 1]), kScale, neg_m));
+                    }
+                    psum += p0 + p1;
+                    pk[i >> 1] = OpTraits<OpT>::pack2(p0, p1);
+                }
+            }
+            l_run += psum;
+        }
+        // ---- P_j -> smem once P_{j-1} V_{j-1} has retired (it read the P buffer and V_{j-1}) ------------
+        if (j > 0) { tc::mbar_wait(bar_o, (j - 1) & 1); tc::fence_after_sync(); }
+        if (row_live) {
+            // 64-key sub-tile c, 16-byte chunks XOR-swizzled with row % 8
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                if (c * 64 < nk) {
+                    uint8_t* prow = gP + c * kTileBytes + tid * 128;
+#pragma unroll
+                    for (int g = 0; g < 8; ++g) {
+                        uint4 u = make_uint4(pk[c * 32 + g * 4 + 0], pk[c * 32 + g * 4 + 1], pk[c * 32 + g * 4 + 2],
+                                             pk[c * 32 + g * 4 + 3]);
+                        *reinterpret_cast<uint4*>(prow + ((g ^ (tid & 7)) << 4)) = u;
+                    }
+                }
             }
         }
-        l_run = l_run * alpha + psum;
         tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the tensor core
         tc::fence_before_sync();
         __syncthreads();
         if (tid == 0) {
             tc::fence_after_sync();
+            if (j + 1 < nkv) {                              // V_{j-1}'s buffer is free: fetch V_{j+1}
+                const int nb = (j + 1) & 1;
+                tc::mbar_arrive_expect_tx(bar_v(nb), kTileBytes);
+                tc::tma_load_2d(sV(nb), &tmap_qkv, bar_v(nb), col_v, t.seg_start + (j + 1) * kKT);
+            }
+            tc::mbar_wait(bar_v(j & 1), (j >> 1) & 1);
+            tc::fence_after_sync();
             const uint32_t idesc = tc::make_idesc(kFmt, kQT, kHd, 0, 1);
-            const uint64_t b0 = tc::smem_desc_mnmajor_sw128(sV(buf));
+            const uint64_t b0 = tc::smem_desc_mnmajor_sw128(sV(j & 1));
             const int ks = nk / 16;
             for (int k = 0; k < ks; ++k) {
                 const uint64_t a = tc::smem_desc_kmajor_sw128(sP + (k >> 2) * kTileBytes) + 2 * (k & 3);
-                tc::mma_f16_ss(tmem + 128, a, b0 + (uint64_t)k * 128, idesc, k != 0);   // 16 key rows = 2048 B
+                tc::mma_f16_ss(tmem + 128, a, b0 + (uint64_t)k * 128, idesc, (j | k) != 0);   // 16 key rows = 2048 B
             }
             tc::mma_commit(bar_o);
         }
-        tc::mbar_wait(bar_o, j & 1);
-        tc::fence_after_sync();
+        __syncwarp();
+    }
+
+    // ---- epilogue: O / l -> 16-bit rows ---------------------------------------------------------------
+    tc::mbar_wait(bar_o, (nkv - 1) & 1);
+    tc::fence_after_sync();
+    const int row = t.q0 + tid;
+    if (row_live) {
+        const float inv = 1.0f / l_run;
+        OpT* dst = out + (size_t)row * d_model + head * kHd;
 #pragma unroll
         for (int c = 0; c < kHd; c += 32) {
             uint32_t r[32];
             tc::tmem_ld_32x32b_x32(t_row + 128 + c, r);
             tc::tmem_ld_wait();
+            if (row < t.seg_end) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) o[c + i] = fmaf(o[c + i], alpha, __uint_as_float(r[i]));
-        }
-        tc::fence_before_sync();
-    }
-
-    const int row = t.q0 + tid;
-    if (row < t.seg_end) {
-        const float inv = 1.0f / l_run;
-        OpT* dst = out + (size_t)row * d_model + head * kHd;
-#pragma unroll
-        for (int g = 0; g < kHd / 8; ++g) {
-            uint4 u;
-            u.x = OpTraits<OpT>::pack2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv);
-            u.y = OpTraits<OpT>::pack2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv);
-            u.z = OpTraits<OpT>::pack2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv);
-            u.w = OpTraits<OpT>::pack2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv);
-            *reinterpret_cast<uint4*>(dst + g * 8) = u;
+                for (int g = 0; g < 4; ++g) {
+                    uint4 u;
+                    u.x = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+                    u.y = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+                    u.z = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+                    u.w = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+                    *reinterpret_cast<uint4*>(dst + c + g * 8) = u;
+                }
+            }
         }
     }
+    tc::fence_before_sync();
     __syncthreads();
     if (warp == 0) tc::tmem_dealloc<kAttnTmemCols>(tmem);
 }
