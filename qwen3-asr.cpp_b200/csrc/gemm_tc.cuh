@@ -55,13 +55,19 @@ using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes : 
                              Epi::kStaged ? (Epi::kResidual ? 3 : 2) : 0>;
 
 // ---- A-operand coordinate policies (m128 = index of this CTA's 128-row block) -----------------
+// The producer and the MMA issuer walk the K blocks of a tile with a small iterator that is advanced
+// incrementally: both loops run on a single thread and every integer division in them is latency on the
+// critical issue path (the first pair version spent ~1000 clk per K block in the MMA loop, profiles/r1b).
 // Linear: A is [M][K] row-major, tensor map dims {K, M}, box {64, 128}.
 struct LoaderLinear {
     int num_k_blocks;
-    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m128, int kb) const {
-        tc::tma_load_2d_pair(dst, tmap, bar, kb * kBlockK, m128 * kBlockM);
+    struct It { int kb; };
+    __device__ __forceinline__ It begin() const { return It{0}; }
+    __device__ __forceinline__ void next(It& it) const { ++it.kb; }
+    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m128, const It& it) const {
+        tc::tma_load_2d_pair(dst, tmap, bar, it.kb * kBlockK, m128 * kBlockM);
     }
-    __device__ __forceinline__ int k_steps(int) const { return kBlockK / kUmmaK; }
+    __device__ __forceinline__ int k_steps(const It&) const { return kBlockK / kUmmaK; }
 };
 // Conv (3x3, stride 2, pad 1) over parity-split planes (layout in stem.h): tensor map dims
 // {C, Fh, R, 4 planes}, box {64, Fh, 128/Fh, 1}.  Output row m = R_out * Fh + of where R_out indexes
@@ -75,15 +81,18 @@ struct LoaderConv {
     int c_blocks;           // ceil(C / 64)
     int rows_per_tile;      // 128 / Fh
     int last_block_steps;   // k-steps that hold real channels in the last channel block of a tap
-    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m128, int kb) const {
-        const int tap = kb / c_blocks, cb = kb - tap * c_blocks;
-        const int dt = tap / 3, df = tap - dt * 3;
-        const int plane = ((dt != 1) ? 2 : 0) + ((df != 1) ? 1 : 0);
-        tc::tma_load_4d_pair(dst, tmap, bar, cb * kBlockK, (df == 0) ? -1 : 0,
-                             m128 * rows_per_tile + ((dt == 0) ? -1 : 0), plane);
+    struct It { int cb, df, dt; };
+    __device__ __forceinline__ It begin() const { return It{0, 0, 0}; }
+    __device__ __forceinline__ void next(It& it) const {
+        if (++it.cb == c_blocks) { it.cb = 0; if (++it.df == 3) { it.df = 0; ++it.dt; } }
     }
-    __device__ __forceinline__ int k_steps(int kb) const {
-        return ((kb % c_blocks) == c_blocks - 1) ? last_block_steps : kBlockK / kUmmaK;
+    __device__ __forceinline__ void load_a(uint32_t dst, const void* tmap, uint32_t bar, int m128, const It& it) const {
+        const int plane = ((it.dt != 1) ? 2 : 0) + ((it.df != 1) ? 1 : 0);
+        tc::tma_load_4d_pair(dst, tmap, bar, it.cb * kBlockK, (it.df == 0) ? -1 : 0,
+                             m128 * rows_per_tile + ((it.dt == 0) ? -1 : 0), plane);
+    }
+    __device__ __forceinline__ int k_steps(const It& it) const {
+        return (it.cb == c_blocks - 1) ? last_block_steps : kBlockK / kUmmaK;
     }
 };
 
@@ -162,62 +171,65 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t tmem_base = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ===================== TMA producer (both CTAs) =====================
+        // ===================== TMA producer (one thread, both CTAs) =====================
         if (lane == 0) {
-            uint32_t it = 0;
+            int s = 0;
+            uint32_t ph = 0;
+            const int b_row0 = (int)rank * (BLOCK_N / 2);
             for (int tile = pair; tile < num_tiles; tile += num_pairs) {
                 // n fastest: pairs running side by side share the A tile through L2
                 const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
                 const int m128 = 2 * m_blk + (int)rank;
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1;
+                const int b_row = n_blk * BLOCK_N + b_row0;
+                typename Loader::It li = loader.begin();
+                for (int kb = 0; kb < num_kb; ++kb) {
                     tc::mbar_wait(empty_bar(s), ph ^ 1);
                     const uint32_t a_dst = smem_base + s * S::kStageBytes;
-                    const uint32_t b_dst = a_dst + S::kABytes;
                     if (rank == 0) tc::mbar_arrive_expect_tx(full_bar(s), 2 * S::kStageBytes);
                     const uint32_t bar = tc::mapa(full_bar(s), 0);
-                    loader.load_a(a_dst, &tmap_a, bar, m128, kb);
-                    tc::tma_load_2d_pair(b_dst, &tmap_b, bar, kb * kBlockK, n_blk * BLOCK_N + (int)rank * (BLOCK_N / 2));
+                    loader.load_a(a_dst, &tmap_a, bar, m128, li);
+                    tc::tma_load_2d_pair(a_dst + S::kABytes, &tmap_b, bar, kb * kBlockK, b_row);
+                    loader.next(li);
+                    if (++s == kStages) { s = 0; ph ^= 1; }
                 }
             }
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===================== MMA issuer (leader CTA) =====================
-        if (rank == 0) {
+        // ===================== MMA issuer (one thread of the leader CTA) =====================
+        if (rank == 0 && lane == 0) {
             constexpr uint32_t idesc = tc::make_idesc(kFmt, 2 * kBlockM, BLOCK_N, 0, 0);
-            uint32_t it = 0, local = 0;
+            const uint64_t desc_hi = tc::smem_desc_kmajor_sw128(0);           // everything but the start address
+            int s = 0;
+            uint32_t ph = 0, local = 0;
             for (int tile = pair; tile < num_tiles; tile += num_pairs, ++local) {
                 const int as = local & 1;
                 const uint32_t aph = (local >> 1) & 1;
                 tc::mbar_wait(tempty_bar(as), aph ^ 1);
                 tc::fence_after_sync();
                 const uint32_t d_tmem = tmem_base + as * 256;
-                for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                    const int s = it % kStages;
-                    const uint32_t ph = (it / kStages) & 1;
+                typename Loader::It li = loader.begin();
+                uint32_t acc = 0;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    const int steps = loader.k_steps(li);
+                    const uint32_t a_addr = smem_base + s * S::kStageBytes;
+                    const uint64_t a_desc = desc_hi | (uint64_t)((a_addr >> 4) & 0x3FFF);
+                    const uint64_t b_desc = desc_hi | (uint64_t)(((a_addr + S::kABytes) >> 4) & 0x3FFF);
                     tc::mbar_wait(full_bar(s), ph);
                     tc::fence_after_sync();
-                    if (lane == 0) {
-                        const uint32_t a_addr = smem_base + s * S::kStageBytes;
-                        const uint32_t b_addr = a_addr + S::kABytes;
-                        const uint64_t a_desc = tc::smem_desc_kmajor_sw128(a_addr);
-                        const uint64_t b_desc = tc::smem_desc_kmajor_sw128(b_addr);
-                        const int steps = loader.k_steps(kb);
 #pragma unroll
-                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-                            // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
-                            if (k < steps)
-                                tc::mma_f16_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
-                        }
-                        tc::mma_commit_pair(empty_bar(s), 3);                        // frees the slot in both CTAs
-                        if (kb == num_kb - 1) tc::mma_commit_pair(tfull_bar(as), 3);   // accumulators complete
+                    for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                        // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
+                        if (k < steps) { tc::mma_f16_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, acc); acc = 1; }
                     }
-                    __syncwarp();
+                    tc::mma_commit_pair(empty_bar(s), 3);                        // frees the slot in both CTAs
+                    loader.next(li);
+                    if (++s == kStages) { s = 0; ph ^= 1; }
                 }
+                tc::mma_commit_pair(tfull_bar(as), 3);                           // accumulators complete
             }
         }
+        __syncwarp();
     } else if (warp >= 4) {
         // ===================== epilogue (both CTAs) =====================
         const int ew = warp - 4;
