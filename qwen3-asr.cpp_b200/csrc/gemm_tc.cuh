@@ -171,33 +171,33 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const uint32_t tmem_base = *tmem_slot_ptr;
 
     if (warp == 0) {
-        // ===================== TMA producer (one thread, both CTAs) =====================
-        if (lane == 0) {
-            int s = 0;
-            uint32_t ph = 0;
-            const int b_row0 = (int)rank * (BLOCK_N / 2);
-            for (int tile = pair; tile < num_tiles; tile += num_pairs) {
-                // n fastest: pairs running side by side share the A tile through L2
-                const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
-                const int m128 = 2 * m_blk + (int)rank;
-                const int b_row = n_blk * BLOCK_N + b_row0;
-                typename Loader::It li = loader.begin();
-                for (int kb = 0; kb < num_kb; ++kb) {
-                    tc::mbar_wait(empty_bar(s), ph ^ 1);
+        // ===================== TMA producer (both CTAs; converged warp, one elected lane issues) ==========
+        int s = 0;
+        uint32_t ph = 0;
+        const int b_row0 = (int)rank * (BLOCK_N / 2);
+        for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+            // n fastest: pairs running side by side share the A tile through L2
+            const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
+            const int m128 = 2 * m_blk + (int)rank;
+            const int b_row = n_blk * BLOCK_N + b_row0;
+            typename Loader::It li = loader.begin();
+            for (int kb = 0; kb < num_kb; ++kb) {
+                tc::mbar_wait(empty_bar(s), ph ^ 1);
+                if (tc::elect_one()) {
                     const uint32_t a_dst = smem_base + s * S::kStageBytes;
                     if (rank == 0) tc::mbar_arrive_expect_tx(full_bar(s), 2 * S::kStageBytes);
                     const uint32_t bar = tc::mapa(full_bar(s), 0);
                     loader.load_a(a_dst, &tmap_a, bar, m128, li);
                     tc::tma_load_2d_pair(a_dst + S::kABytes, &tmap_b, bar, kb * kBlockK, b_row);
-                    loader.next(li);
-                    if (++s == kStages) { s = 0; ph ^= 1; }
                 }
+                __syncwarp();
+                loader.next(li);
+                if (++s == kStages) { s = 0; ph ^= 1; }
             }
         }
-        __syncwarp();
     } else if (warp == 1) {
-        // ===================== MMA issuer (one thread of the leader CTA) =====================
-        if (rank == 0 && lane == 0) {
+        // ===================== MMA issuer (leader CTA; the warp stays converged, one elected lane issues) ====
+        if (rank == 0) {
             constexpr uint32_t idesc = tc::make_idesc(kFmt, 2 * kBlockM, BLOCK_N, 0, 0);
             const uint64_t desc_hi = tc::smem_desc_kmajor_sw128(0);           // everything but the start address
             int s = 0;
@@ -217,19 +217,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                     const uint64_t b_desc = desc_hi | (uint64_t)(((a_addr + S::kABytes) >> 4) & 0x3FFF);
                     tc::mbar_wait(full_bar(s), ph);
                     tc::fence_after_sync();
+                    if (tc::elect_one()) {
 #pragma unroll
-                    for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-                        // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
-                        if (k < steps) { tc::mma_f16_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, acc); acc = 1; }
+                        for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+                            // advance 16 elements (32 B) along K inside the swizzle span: +2 in (addr>>4) units
+                            if (k < steps) tc::mma_f16_ss_pair(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, acc | k);
+                        }
+                        tc::mma_commit_pair(empty_bar(s), 3);                    // frees the slot in both CTAs
                     }
-                    tc::mma_commit_pair(empty_bar(s), 3);                        // frees the slot in both CTAs
+                    __syncwarp();
+                    acc = 1;
                     loader.next(li);
                     if (++s == kStages) { s = 0; ph ^= 1; }
                 }
-                tc::mma_commit_pair(tfull_bar(as), 3);                           // accumulators complete
+                if (tc::elect_one()) tc::mma_commit_pair(tfull_bar(as), 3);      // accumulators complete
+                __syncwarp();
             }
         }
-        __syncwarp();
     } else if (warp >= 4) {
         // ===================== epilogue (both CTAs) =====================
         const int ew = warp - 4;
