@@ -1,0 +1,63 @@
+"""The C++ shim headers (include/q3a/*.h) compile with plain g++ -std=c++17 against libq3a.so and behave like
+the reference's entry points: CPU part checks the build and the loud failure without a GPU; GPU part runs the
+harness the way Qwen3ASR::transcribe_internal would and compares with the oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "qwen3-asr.cpp_b200")
+
+
+@pytest.fixture(scope="module")
+def harness(tmp_path_factory):
+    out = str(tmp_path_factory.mktemp("shim") / "shim_harness")
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "shim_harness.cpp"), "-o", out, "-L", PKG, "-lq3a", f"-Wl,-rpath,{PKG}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "warning" not in r.stderr, r.stderr
+    return out
+
+
+def test_shim_compiles_and_fails_loudly_without_gpu(lib, harness, tmp_path):
+    from q3a_b200 import synth
+    pcm = synth.synth_audio(5, 16000)
+    p = tmp_path / "a.f32"
+    pcm.tofile(p)
+    r = subprocess.run([harness, str(p), "-", str(tmp_path / "mel.f32"), str(tmp_path / "feat.f32")],
+                       capture_output=True, text=True)
+    if lib.q3a_device_count() == 0:
+        assert r.returncode == 2 and "no CUDA device" in r.stderr       # no CPU fallback
+    else:
+        assert r.returncode == 0, r.stderr
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["asr", "aligner"])
+def test_shim_matches_oracle(lib, harness, tmp_path, mode):
+    from q3a_b200 import synth
+    from oracle import encoder_oracle as EO, mel_oracle as MO
+    shape = synth.tiny_shape()
+    w = synth.random_weights(shape, 11)
+    gguf = synth.write_gguf(str(tmp_path / "tiny.gguf"), shape, w, "f16")
+    pcm = synth.synth_audio(6, 16000 * 3 + 1234)
+    p = tmp_path / "a.f32"
+    pcm.tofile(p)
+    r = subprocess.run([harness, str(p), gguf, str(tmp_path / "mel.f32"), str(tmp_path / "feat.f32"), mode],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    assert "Mel bins mismatch: expected 128, got 64" in r.stdout        # audio_encoder.cpp:321-325
+    filt = MO.mel_filters_numpy()
+    want_mel = MO.log_mel_numpy(pcm, filt)
+    mel = np.fromfile(tmp_path / "mel.f32", dtype=np.float32).reshape(want_mel.shape)
+    assert np.abs(mel - want_mel).max() <= 1e-4
+    W = EO.Weights(synth.stored_weights(w, "f16"), "f16")
+    want = EO.encode(want_mel, W, n_layers=shape.n_layers, d_model=shape.d_model, n_heads=shape.n_heads,
+                     variant="asr" if mode == "asr" else "aligner")
+    got = np.fromfile(tmp_path / "feat.f32", dtype=np.float32).reshape(want.shape)
+    cos = float((got * want).sum() / (np.linalg.norm(got) * np.linalg.norm(want)))
+    rel = float(np.abs(got - want).max() / np.abs(want).max())
+    assert cos >= 0.999 and rel <= 1e-2, (cos, rel)
