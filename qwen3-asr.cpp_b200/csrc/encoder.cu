@@ -49,6 +49,10 @@ struct ArenaPlan {
         std::memcpy(it.bytes.data(), v.data(), it.bytes.size());
         items.push_back(std::move(it));
     }
+    void add_raw(const void** slot, const std::vector<uint8_t>& v) {
+        Item it; it.slot = slot; it.bytes = v;
+        items.push_back(std::move(it));
+    }
     void add_op(const void** slot, const std::vector<float>& v, int fmt) {
         Item it; it.slot = slot;
         it.bytes.resize(v.size() * 2);
@@ -249,7 +253,11 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     const int sp_stem = prof.begin(SP_STEM);
     {
         const int sp = prof.begin(SP_OTHER);
-        Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks, n_chunks, P2, max_dev, e->conv1_w, e->conv1_b, C, planes1, ps1, st));
+        if (e->conv1_wimg)
+            Q3A_TRY(conv1_tc_launch<OpT>(mel_dev, d_chunks, n_chunks, P2, max_dev, e->conv1_wimg, e->conv1_b, C, planes1,
+                                         e->rcap1, st));
+        else
+            Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks, n_chunks, P2, max_dev, e->conv1_w, e->conv1_b, C, planes1, ps1, st));
         prof.end(sp);
     }
     {
@@ -389,6 +397,11 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
 #define FETCH(name, vec, n) do { if (!fetch(f, P + (name), vec, err, (n))) { set_error(err); return Q3A_ERR_FORMAT; } } while (0)
     // conv1: [C][1][3 mel][3 time] -> f32 [C][9] unchanged (index df*3 + dt)
     FETCH("conv1.weight", v, (int64_t)C * 9);  plan.add_f32(&e->conv1_w, v);
+    if (conv1_tc_supported(C)) {
+        std::vector<uint8_t> img;
+        conv1_tc_weight_image(v.data(), C, img);
+        plan.add_raw(&e->conv1_wimg, img);
+    }
     FETCH("conv1.bias", v, C);                 plan.add_f32(&e->conv1_b, v);
     // conv2/3: [OC][IC][3 mel (df)][3 time (dt)] -> [OC][tap = dt*3 + df][cpad] (gemm_tc.cuh LoaderConv)
     const int cpad = (C + 63) / 64 * 64;

@@ -18,6 +18,7 @@ struct q3a_encoder {
     size_t arena_used = 0;
     const float *conv1_w = nullptr, *conv1_b = nullptr, *conv2_b = nullptr, *conv3_b = nullptr;
     const void *conv2_w = nullptr, *conv3_w = nullptr, *conv_out_w = nullptr;
+    const void* conv1_wimg = nullptr;   // smem image of the conv1 weights for conv1_tc_kernel (null: CUDA-core conv1)
     struct Layer {
         const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_o, *b_up, *b_down;
         const void *w_qkv, *w_o, *w_up, *w_down;

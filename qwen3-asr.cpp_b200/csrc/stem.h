@@ -28,6 +28,14 @@ int conv1_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks, in
                  const float* w /*[C][9]: df*3+dt*/, const float* bias, int C, OpT* planes, long long plane_stride,
                  cudaStream_t stream);
 
+// Tensor-core conv1 (conv1_tc.cu): same result layout; used whenever the channel count fits (C % 32 == 0, C <= 512).
+// w_image: device copy of conv1_tc_weight_image(); R_cap: rows per plane of `planes` (plane stride = R_cap*32*C).
+bool conv1_tc_supported(int C);
+void conv1_tc_weight_image(const float* w /*[C][9]: df*3+dt*/, int C, std::vector<uint8_t>& image);
+template <class OpT>
+int conv1_tc_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks, int P2, const float* clip_max,
+                    const void* w_image, const float* bias, int C, OpT* planes, int R_cap, cudaStream_t stream);
+
 // LayerNorm over rows of x [T][d] f32 -> 16-bit operand rows (audio_encoder.cpp:441-448)
 template <class OpT>
 int layernorm_launch(const float* x, const float* gamma, const float* beta, float eps, int T, int d, OpT* out,
