@@ -60,45 +60,55 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
     const int col_q = head * kHd, col_k = d_model + head * kHd, col_v = 2 * d_model + head * kHd;
     constexpr int kFmt = OpTraits<OpT>::kFmt;
 
-    if (tid == 0) {
-        tc::prefetch_tmap(&tmap_qkv);
-        tc::mbar_init(bar_q, 1); tc::mbar_init(bar_s, 1); tc::mbar_init(bar_o, 1);
-        tc::mbar_init(bar_k(0), 1); tc::mbar_init(bar_k(1), 1);
-        tc::mbar_init(bar_v(0), 1); tc::mbar_init(bar_v(1), 1);
-        tc::fence_barrier_init();
-    }
-    if (warp == 0) tc::tmem_alloc<kAttnTmemCols>(tmem_slot);
-    tc::fence_before_sync();
-    __syncthreads();
-    tc::fence_after_sync();
-    const uint32_t tmem = *tmem_slot_ptr;
-    const uint32_t t_row = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane quadrant
-
+    uint32_t tmem = 0;
     auto keys_of = [&](int j) {                                      // keys block j feeds to the MMAs
         const int rem = seg_len - j * kKT;
         return rem >= kKT ? kKT : ((rem + 15) & ~15);
     };
-    auto issue_qk = [&](int j) {                                     // tid 0 only
+    // Warp 0 is also the issue warp.  It stays converged: barrier waits and descriptor arithmetic are
+    // warp-uniform and only the TMA / tcgen05 instructions themselves sit under elect.sync, so the
+    // UTCHMMAs go out back to back (a lone `tid == 0` branch takes ~1000 clk per block to issue).
+    auto issue_qk = [&](int j) {                                     // warp 0, converged
         tc::mbar_wait(bar_k(j & 1), (j >> 1) & 1);
         tc::fence_after_sync();
         const uint32_t idesc = tc::make_idesc(kFmt, kQT, keys_of(j), 0, 0);
         const uint64_t a = tc::smem_desc_kmajor_sw128(sQ), b = tc::smem_desc_kmajor_sw128(sK(j & 1));
+        if (tc::elect_one()) {
 #pragma unroll
-        for (int k = 0; k < kHd / 16; ++k) tc::mma_f16_ss(tmem, a + 2 * k, b + 2 * k, idesc, k != 0);
-        tc::mma_commit(bar_s);
+            for (int k = 0; k < kHd / 16; ++k) tc::mma_f16_ss(tmem, a + 2 * k, b + 2 * k, idesc, k != 0);
+            tc::mma_commit(bar_s);
+        }
+        __syncwarp();
     };
 
-    if (tid == 0) {
-        tc::mbar_arrive_expect_tx(bar_q, kTileBytes);
-        tc::tma_load_2d(sQ, &tmap_qkv, bar_q, col_q, t.q0);
-        tc::mbar_arrive_expect_tx(bar_k(0), kTileBytes);
-        tc::tma_load_2d(sK(0), &tmap_qkv, bar_k(0), col_k, t.seg_start);
-        tc::mbar_arrive_expect_tx(bar_v(0), kTileBytes);
-        tc::tma_load_2d(sV(0), &tmap_qkv, bar_v(0), col_v, t.seg_start);
-        if (nkv > 1) {
-            tc::mbar_arrive_expect_tx(bar_k(1), kTileBytes);
-            tc::tma_load_2d(sK(1), &tmap_qkv, bar_k(1), col_k, t.seg_start + kKT);
+    if (warp == 0) {
+        // barriers, first loads, then the TMEM allocation: the fetch latency runs under it
+        if (tc::elect_one()) {
+            tc::prefetch_tmap(&tmap_qkv);
+            tc::mbar_init(bar_q, 1); tc::mbar_init(bar_s, 1); tc::mbar_init(bar_o, 1);
+            tc::mbar_init(bar_k(0), 1); tc::mbar_init(bar_k(1), 1);
+            tc::mbar_init(bar_v(0), 1); tc::mbar_init(bar_v(1), 1);
+            tc::fence_barrier_init();
+            tc::mbar_arrive_expect_tx(bar_q, kTileBytes);
+            tc::tma_load_2d(sQ, &tmap_qkv, bar_q, col_q, t.q0);
+            tc::mbar_arrive_expect_tx(bar_k(0), kTileBytes);
+            tc::tma_load_2d(sK(0), &tmap_qkv, bar_k(0), col_k, t.seg_start);
+            tc::mbar_arrive_expect_tx(bar_v(0), kTileBytes);
+            tc::tma_load_2d(sV(0), &tmap_qkv, bar_v(0), col_v, t.seg_start);
+            if (nkv > 1) {
+                tc::mbar_arrive_expect_tx(bar_k(1), kTileBytes);
+                tc::tma_load_2d(sK(1), &tmap_qkv, bar_k(1), col_k, t.seg_start + kKT);
+            }
         }
+        __syncwarp();
+        tc::tmem_alloc<kAttnTmemCols>(tmem_slot);
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    tmem = *tmem_slot_ptr;
+    const uint32_t t_row = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane quadrant
+    if (warp == 0) {
         tc::mbar_wait(bar_q, 0);
         issue_qk(0);
     }
@@ -123,29 +133,45 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
         }
         tc::fence_before_sync();
         __syncthreads();                                   // S is in registers everywhere: TMEM S and K_j are free
-        if (tid == 0) {
+        if (warp == 0) {
             tc::fence_after_sync();
             if (j + 2 < nkv) {
-                tc::mbar_arrive_expect_tx(bar_k(j & 1), kTileBytes);
-                tc::tma_load_2d(sK(j & 1), &tmap_qkv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
+                if (tc::elect_one()) {
+                    tc::mbar_arrive_expect_tx(bar_k(j & 1), kTileBytes);
+                    tc::tma_load_2d(sK(j & 1), &tmap_qkv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
+                }
+                __syncwarp();
             }
             if (j + 1 < nkv) issue_qk(j + 1);
         }
-        __syncwarp();
         // ---- softmax on registers -------------------------------------------------------------------
         float psum = 0.0f;
-        uint32_t pk[64];                                   // P row, packed 16-bit pairs
+        uint32_t* pk = s;                                  // P row, packed 16-bit pairs, overwrites consumed scores in place
         if (row_live) {
-            float mx = -INFINITY;
+            float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;   // independent chains
             if (n_valid == kKT) {
 #pragma unroll
-                for (int i = 0; i < 128; ++i) mx = fmaxf(mx, __uint_as_float(s[i]));
+                for (int i = 0; i < 128; i += 8) {
+                    mx0 = fmaxf(mx0, fmaxf(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])));
+                    mx1 = fmaxf(mx1, fmaxf(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])));
+                    mx2 = fmaxf(mx2, fmaxf(__uint_as_float(s[i + 4]), __uint_as_float(s[i + 5])));
+                    mx3 = fmaxf(mx3, fmaxf(__uint_as_float(s[i + 6]), __uint_as_float(s[i + 7])));
+                }
             } else {
 #pragma unroll
-                for (int i = 0; i < 128; ++i)
-                    if (i < nk && i < n_valid) mx = fmaxf(mx, __uint_as_float(s[i]));
+                for (int i = 0; i < 128; i += 16) {
+                    if (i < nk) {                          // warp-uniform: 16-key groups past the end are skipped
+#pragma unroll
+                        for (int e = 0; e < 16; e += 4) {
+                            if (i + e + 0 < n_valid) mx0 = fmaxf(mx0, __uint_as_float(s[i + e + 0]));
+                            if (i + e + 1 < n_valid) mx1 = fmaxf(mx1, __uint_as_float(s[i + e + 1]));
+                            if (i + e + 2 < n_valid) mx2 = fmaxf(mx2, __uint_as_float(s[i + e + 2]));
+                            if (i + e + 3 < n_valid) mx3 = fmaxf(mx3, __uint_as_float(s[i + e + 3]));
+                        }
+                    }
+                }
             }
-            mx *= kScale;
+            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * kScale;
             if (j == 0) {
                 m_ref = mx;
             } else {
@@ -171,23 +197,28 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             }
             const float neg_m = -m_ref;
             if (n_valid == kKT) {
+                float ps1 = 0.0f;
 #pragma unroll
                 for (int i = 0; i < 128; i += 2) {
                     const float p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i]), kScale, neg_m));
                     const float p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + 1]), kScale, neg_m));
-                    psum += p0 + p1;
+                    psum += p0; ps1 += p1;
                     pk[i >> 1] = OpTraits<OpT>::pack2(p0, p1);
                 }
+                psum += ps1;
             } else {
 #pragma unroll
-                for (int i = 0; i < 128; i += 2) {
-                    float p0 = 0.0f, p1 = 0.0f;
-                    if (i < nk) {
-                        if (i < n_valid) p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i]), kScale, neg_m));
-                        if (i + 1 < n_valid) p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + 1]), kScale, neg_m));
+                for (int i = 0; i < 128; i += 16) {
+                    if (i < nk) {                          // warp-uniform; P columns >= nk are never read
+#pragma unroll
+                        for (int e = 0; e < 16; e += 2) {
+                            float p0 = 0.0f, p1 = 0.0f;
+                            if (i + e < n_valid) p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i + e]), kScale, neg_m));
+                            if (i + e + 1 < n_valid) p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + e + 1]), kScale, neg_m));
+                            psum += p0 + p1;
+                            pk[(i + e) >> 1] = OpTraits<OpT>::pack2(p0, p1);
+                        }
                     }
-                    psum += p0 + p1;
-                    pk[i >> 1] = OpTraits<OpT>::pack2(p0, p1);
                 }
             }
             l_run += psum;
@@ -202,6 +233,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
                     uint8_t* prow = gP + c * kTileBytes + tid * 128;
 #pragma unroll
                     for (int g = 0; g < 8; ++g) {
+                        if (c * 64 + g * 8 >= nk) break;
                         uint4 u = make_uint4(pk[c * 32 + g * 4 + 0], pk[c * 32 + g * 4 + 1], pk[c * 32 + g * 4 + 2],
                                              pk[c * 32 + g * 4 + 3]);
                         *reinterpret_cast<uint4*>(prow + ((g ^ (tid & 7)) << 4)) = u;
@@ -212,25 +244,31 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
         tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the tensor core
         tc::fence_before_sync();
         __syncthreads();
-        if (tid == 0) {
+        if (warp == 0) {
             tc::fence_after_sync();
             if (j + 1 < nkv) {                              // V_{j-1}'s buffer is free: fetch V_{j+1}
                 const int nb = (j + 1) & 1;
-                tc::mbar_arrive_expect_tx(bar_v(nb), kTileBytes);
-                tc::tma_load_2d(sV(nb), &tmap_qkv, bar_v(nb), col_v, t.seg_start + (j + 1) * kKT);
+                if (tc::elect_one()) {
+                    tc::mbar_arrive_expect_tx(bar_v(nb), kTileBytes);
+                    tc::tma_load_2d(sV(nb), &tmap_qkv, bar_v(nb), col_v, t.seg_start + (j + 1) * kKT);
+                }
+                __syncwarp();
             }
             tc::mbar_wait(bar_v(j & 1), (j >> 1) & 1);
             tc::fence_after_sync();
             const uint32_t idesc = tc::make_idesc(kFmt, kQT, kHd, 0, 1);
             const uint64_t b0 = tc::smem_desc_mnmajor_sw128(sV(j & 1));
+            const uint64_t a0 = tc::smem_desc_kmajor_sw128(sP), a1 = tc::smem_desc_kmajor_sw128(sP + kTileBytes);
             const int ks = nk / 16;
-            for (int k = 0; k < ks; ++k) {
-                const uint64_t a = tc::smem_desc_kmajor_sw128(sP + (k >> 2) * kTileBytes) + 2 * (k & 3);
-                tc::mma_f16_ss(tmem + 128, a, b0 + (uint64_t)k * 128, idesc, (j | k) != 0);   // 16 key rows = 2048 B
+            if (tc::elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k)                 // 16 key rows of V = 2048 B
+                    if (k < ks) tc::mma_f16_ss(tmem + 128, (k < 4 ? a0 : a1) + 2 * (k & 3), b0 + (uint64_t)k * 128, idesc,
+                                               (j | k) != 0);
+                tc::mma_commit(bar_o);
             }
-            tc::mma_commit(bar_o);
+            __syncwarp();
         }
-        __syncwarp();
     }
 
     // ---- epilogue: O / l -> 16-bit rows ---------------------------------------------------------------
@@ -313,14 +351,15 @@ extern "C" int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int
     std::vector<AttnTile> tiles;
     attention_tiles(cu_seqlens, n_seg, tiles);
     if (tiles.empty()) return Q3A_OK;
-    AttnTile* d_tiles = nullptr;
-    Q3A_CUDA(cudaMalloc(&d_tiles, sizeof(AttnTile) * tiles.size()));
+    static DevBuf d_tiles_buf;                       // test-only entry point: grow-only scratch, never freed
+    Q3A_TRY(d_tiles_buf.reserve(sizeof(AttnTile) * tiles.size()));
+    AttnTile* d_tiles = d_tiles_buf.as<AttnTile>();
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // pageable source: the runtime stages the table before returning, so `tiles` may go out of scope
     cudaError_t e = cudaMemcpyAsync(d_tiles, tiles.data(), sizeof(AttnTile) * tiles.size(), cudaMemcpyHostToDevice, st);
     int rc = Q3A_OK;
     if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = Q3A_ERR_CUDA; }
     if (rc == Q3A_OK) rc = attention_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, st);
-    cudaStreamSynchronize(st);
-    cudaFree(d_tiles);
+    if (!st) cudaStreamSynchronize(st);               // with a caller's stream the call stays asynchronous
     return rc;
 }
