@@ -14,6 +14,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <numeric>
 
@@ -485,9 +486,17 @@ extern "C" void q3a_encoder_free(q3a_encoder* e) {
     e->arena.release(); e->pe.release();
     e->planes1.release(); e->planes2.release(); e->feat.release(); e->x.release(); e->h.release(); e->qkv.release();
     e->att.release(); e->up.release(); e->tables.release(); e->stage_in.release(); e->stage_out.release();
+    e->stage_in2.release(); e->stage_out2.release();
     e->stage_mel.release(); e->stage_max.release();
     e->ring.release();
     for (auto ev : e->ev_pool) cudaEventDestroy(ev);
+    for (int i = 0; i < 2; ++i) {
+        if (e->ev_in[i]) cudaEventDestroy(e->ev_in[i]);
+        if (e->ev_comp[i]) cudaEventDestroy(e->ev_comp[i]);
+        if (e->ev_out[i]) cudaEventDestroy(e->ev_out[i]);
+    }
+    if (e->copy_in) cudaStreamDestroy(e->copy_in);
+    if (e->copy_out) cudaStreamDestroy(e->copy_out);
     if (e->stream) cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -507,8 +516,15 @@ extern "C" int q3a_encoder_load(const char* gguf_path, int device, int operand_d
     q3a_encoder* e = new q3a_encoder();
     e->device = device; e->fmt = operand_dtype;
     int rc = load_weights(e, f);
-    if (rc == Q3A_OK && cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) != cudaSuccess) {
-        set_error("cudaStreamCreate failed"); rc = Q3A_ERR_CUDA;
+    if (rc == Q3A_OK) {
+        bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&e->copy_in, cudaStreamNonBlocking) == cudaSuccess &&
+                  cudaStreamCreateWithFlags(&e->copy_out, cudaStreamNonBlocking) == cudaSuccess;
+        for (int i = 0; i < 2 && ok; ++i)
+            ok = cudaEventCreateWithFlags(&e->ev_in[i], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&e->ev_comp[i], cudaEventDisableTiming) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&e->ev_out[i], cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) { set_error("cudaStreamCreate / cudaEventCreate failed"); rc = Q3A_ERR_CUDA; }
     }
     if (rc != Q3A_OK) { q3a_encoder_free(e); return rc; }
     *out = e;
@@ -540,7 +556,7 @@ extern "C" int q3a_encoder_get_timings(const q3a_encoder* e, q3a_timings* out) {
 extern "C" int64_t q3a_encoder_device_bytes(const q3a_encoder* e) {
     if (!e) return 0;
     return (int64_t)(e->arena.cap + e->pe.cap + e->planes1.cap + e->planes2.cap + e->feat.cap + e->x.cap + e->h.cap +
-                     e->qkv.cap + e->att.cap + e->up.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap +
+                     e->qkv.cap + e->att.cap + e->up.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap + e->stage_in2.cap + e->stage_out2.cap +
                      e->stage_mel.cap + e->stage_max.cap);
 }
 
@@ -557,17 +573,107 @@ extern "C" int q3a_encoder_encode_device(q3a_encoder* e, const float* mel_dev, c
     return prof_collect(e, st);
 }
 
-// Splits [0, n) into passes whose stem workspace stays bounded.
+// Splits [0, n) into passes.  A pass bounds the stem workspace (kMaxChunksPerPass) and is the unit of the
+// upload | compute | download pipeline of the host-pointer entry points: a call with enough work is cut into
+// at least two balanced passes so that the PCIe copies of one pass hide under the kernels of the other.
+// Results do not depend on the split (the kernels are batch-invariant).
+constexpr int kPipelineMinChunks = 640;   // ~8300 tokens: below this a pass no longer fills the GEMM waves
+
+static int pipeline_min_chunks() {          // Q3A_PIPELINE_MIN_CHUNKS overrides (0 disables the split)
+    static const int v = [] {
+        const char* e = getenv("Q3A_PIPELINE_MIN_CHUNKS");
+        const int x = e ? atoi(e) : kPipelineMinChunks;
+        return x > 0 ? x : (1 << 30);
+    }();
+    return v;
+}
+
+static int chunks_of(int n_frames, int mode) {
+    const int c = (n_frames + kChunkFrames - 1) / kChunkFrames;
+    return (mode == Q3A_MODE_ASR || mode == Q3A_MODE_ALIGNER) ? c : c + 1;
+}
+
 static void plan_passes(const int* n_frames, int n, int mode, std::vector<int>& bounds) {
+    long long total = 0;
+    for (int i = 0; i < n; ++i) total += chunks_of(n_frames[i], mode);
+    long long n_pass = (total + kMaxChunksPerPass - 1) / kMaxChunksPerPass;
+    if (n_pass < 2 && total >= 2LL * pipeline_min_chunks()) n_pass = total / pipeline_min_chunks() >= 3 && getenv("Q3A_PIPELINE_3") ? 3 : 2;
+    if (n_pass < 1) n_pass = 1;
+    const long long target = (total + n_pass - 1) / n_pass;
     bounds.assign(1, 0);
-    int chunks = 0;
+    long long chunks = 0;
     for (int i = 0; i < n; ++i) {
-        const int c = (mode == Q3A_MODE_ASR || mode == Q3A_MODE_ALIGNER) ? (n_frames[i] + kChunkFrames - 1) / kChunkFrames
-                                                                          : (n_frames[i] + kChunkFrames - 1) / kChunkFrames + 1;
-        if (chunks > 0 && chunks + c > kMaxChunksPerPass) { bounds.push_back(i); chunks = 0; }
+        const int c = chunks_of(n_frames[i], mode);
+        if (chunks > 0 && (chunks + c > kMaxChunksPerPass || chunks >= target)) { bounds.push_back(i); chunks = 0; }
         chunks += c;
     }
     bounds.push_back(n);
+}
+
+// The pipeline itself.  `in[i]` has `in_elems[i]` floats on the host; `compute(u0, nu, in_dev, in_off, out_dev,
+// tok_off)` enqueues the pass on e->stream and fills tok_off[0..nu] (token rows relative to the pass).
+template <class Compute>
+static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in_elems, const int* n_frames, int n,
+                           int mode, int width, float* const* out, int* n_tokens, Compute compute) {
+    std::vector<int> bounds;
+    plan_passes(n_frames, n, mode, bounds);
+    const int n_pass = (int)bounds.size() - 1;
+    DevBuf* sin[2] = {&e->stage_in, &e->stage_in2};
+    DevBuf* sout[2] = {&e->stage_out, &e->stage_out2};
+    // offsets and buffer sizes of every pass, reserved up front (nothing is in flight yet)
+    std::vector<std::vector<int64_t>> ioff(n_pass);
+    std::vector<int> T(n_pass, 0);
+    size_t need_in[2] = {0, 0}, need_out[2] = {0, 0};
+    for (int p = 0; p < n_pass; ++p) {
+        const int u0 = bounds[p], nu = bounds[p + 1] - u0;
+        q3a_pack_offsets(in_elems + u0, nu, 1, 64, ioff[p]);
+        for (int i = 0; i < nu; ++i) T[p] += encoder_n_tokens(n_frames[u0 + i], mode);
+        need_in[p & 1] = std::max(need_in[p & 1], sizeof(float) * (size_t)(ioff[p][nu] + 64));
+        need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)T[p] * width + 64));
+    }
+    for (int b = 0; b < 2; ++b) {
+        if (need_in[b]) Q3A_TRY(sin[b]->reserve(need_in[b]));
+        if (need_out[b]) Q3A_TRY(sout[b]->reserve(need_out[b]));
+    }
+    auto drain = [&](int rc) {
+        cudaStreamSynchronize(e->copy_in); cudaStreamSynchronize(e->stream); cudaStreamSynchronize(e->copy_out);
+        return rc;
+    };
+#define PIPE_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error(std::string(#x) + ": " + cudaGetErrorString(e_)); return drain(Q3A_ERR_CUDA); } } while (0)
+    auto upload = [&](int p) -> int {
+        const int b = p & 1, u0 = bounds[p], nu = bounds[p + 1] - u0;
+        if (p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->copy_in, e->ev_comp[b], 0));   // pass p-2 has consumed the buffer
+        for (int i = 0; i < nu; ++i)
+            if (in_elems[u0 + i] > 0)
+                PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<float>() + ioff[p][i], in[u0 + i], sizeof(float) * in_elems[u0 + i],
+                                          cudaMemcpyHostToDevice, e->copy_in));
+        PIPE_CUDA(cudaEventRecord(e->ev_in[b], e->copy_in));
+        return Q3A_OK;
+    };
+    if (n_pass > 0) { const int rc = upload(0); if (rc != Q3A_OK) return rc; }
+    for (int p = 0; p < n_pass; ++p) {
+        const int b = p & 1, u0 = bounds[p], nu = bounds[p + 1] - u0;
+        if (p + 1 < n_pass) { const int rc = upload(p + 1); if (rc != Q3A_OK) return rc; }
+        PIPE_CUDA(cudaStreamWaitEvent(e->stream, e->ev_in[b], 0));
+        if (p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->stream, e->ev_out[b], 0));       // pass p-2 has been downloaded
+        std::vector<int64_t> toff(nu + 1, 0);
+        const int rc = compute(u0, nu, sin[b]->as<float>(), ioff[p].data(), sout[b]->as<float>(), toff.data());
+        if (rc != Q3A_OK) return drain(rc);
+        PIPE_CUDA(cudaEventRecord(e->ev_comp[b], e->stream));
+        PIPE_CUDA(cudaStreamWaitEvent(e->copy_out, e->ev_comp[b], 0));
+        for (int i = 0; i < nu; ++i) {
+            const int64_t rows = toff[i + 1] - toff[i];
+            if (n_tokens) n_tokens[u0 + i] = (int)rows;
+            if (rows > 0)
+                PIPE_CUDA(cudaMemcpyAsync(out[u0 + i], sout[b]->as<float>() + toff[i] * width, sizeof(float) * rows * width,
+                                          cudaMemcpyDeviceToHost, e->copy_out));
+        }
+        PIPE_CUDA(cudaEventRecord(e->ev_out[b], e->copy_out));
+    }
+    PIPE_CUDA(cudaStreamSynchronize(e->copy_out));
+    PIPE_CUDA(cudaStreamSynchronize(e->stream));
+#undef PIPE_CUDA
+    return Q3A_OK;
 }
 
 extern "C" int q3a_encoder_encode_batch(q3a_encoder* e, const float* const* mel, int n_mel, const int* n_frames,
@@ -584,36 +690,14 @@ extern "C" int q3a_encoder_encode_batch(q3a_encoder* e, const float* const* mel,
     Q3A_TRY(use_device(e->device));
     g_launch_counter = 0;
     prof_reset(e);
-    cudaStream_t st = e->stream;
     const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
-    std::vector<int> bounds;
-    plan_passes(n_frames, n_utts, mode, bounds);
-    for (size_t p = 0; p + 1 < bounds.size(); ++p) {
-        const int u0 = bounds[p], nu = bounds[p + 1] - u0;
-        std::vector<int> elems(nu);
-        std::vector<int64_t> moff;
-        int T = 0;
-        for (int i = 0; i < nu; ++i) { elems[i] = n_mel * n_frames[u0 + i]; T += encoder_n_tokens(n_frames[u0 + i], mode); }
-        q3a_pack_offsets(elems.data(), nu, 1, 64, moff);
-        Q3A_TRY(e->stage_mel.reserve(sizeof(float) * (size_t)(moff[nu] + 64)));
-        Q3A_TRY(e->stage_out.reserve(sizeof(float) * ((size_t)T * width + 64)));
-        for (int i = 0; i < nu; ++i)
-            if (elems[i] > 0)
-                Q3A_CUDA(cudaMemcpyAsync(e->stage_mel.as<float>() + moff[i], mel[u0 + i], sizeof(float) * elems[i],
-                                         cudaMemcpyHostToDevice, st));
-        std::vector<int64_t> toff(nu + 1);
-        Q3A_TRY(encode_dispatch(e, e->stage_mel.as<float>(), moff.data(), nullptr, n_frames + u0, nu, mode,
-                                e->stage_out.as<float>(), toff.data(), st));
-        for (int i = 0; i < nu; ++i) {
-            const int64_t rows = toff[i + 1] - toff[i];
-            if (n_tokens) n_tokens[u0 + i] = (int)rows;
-            if (rows > 0)
-                Q3A_CUDA(cudaMemcpyAsync(out[u0 + i], e->stage_out.as<float>() + toff[i] * width,
-                                         sizeof(float) * rows * width, cudaMemcpyDeviceToHost, st));
-        }
-        Q3A_CUDA(cudaStreamSynchronize(st));
-    }
-    return prof_collect(e, st);
+    std::vector<int> elems(n_utts);
+    for (int i = 0; i < n_utts; ++i) elems[i] = n_mel * n_frames[i];
+    Q3A_TRY(run_host_passes(e, mel, elems.data(), n_frames, n_utts, mode, width, out, n_tokens,
+                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, int64_t* toff) {
+                                return encode_dispatch(e, in_dev, in_off, nullptr, n_frames + u0, nu, mode, out_dev, toff, e->stream);
+                            }));
+    return prof_collect(e, e->stream);
 }
 
 // mel (raw log10 + per-clip max) and encoder (clamp fused into conv1's loads) for clips on the device
@@ -668,36 +752,14 @@ extern "C" int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* e, const floa
     Q3A_TRY(use_device(e->device));
     g_launch_counter = 0;
     prof_reset(e);
-    cudaStream_t st = e->stream;
     const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
-    std::vector<int> nf(n_clips), bounds;
+    std::vector<int> nf(n_clips);
     for (int i = 0; i < n_clips; ++i) nf[i] = n_samples[i] / 160;
-    plan_passes(nf.data(), n_clips, mode, bounds);
-    for (size_t p = 0; p + 1 < bounds.size(); ++p) {
-        const int u0 = bounds[p], nu = bounds[p + 1] - u0;
-        std::vector<int64_t> poff;
-        int T = 0;
-        for (int i = 0; i < nu; ++i) T += encoder_n_tokens(nf[u0 + i], mode);
-        q3a_pack_offsets(n_samples + u0, nu, 1, 64, poff);
-        Q3A_TRY(e->stage_in.reserve(sizeof(float) * (size_t)(poff[nu] + 64)));
-        Q3A_TRY(e->stage_out.reserve(sizeof(float) * ((size_t)T * width + 64)));
-        for (int i = 0; i < nu; ++i)
-            if (n_samples[u0 + i] > 0)
-                Q3A_CUDA(cudaMemcpyAsync(e->stage_in.as<float>() + poff[i], pcm[u0 + i], sizeof(float) * n_samples[u0 + i],
-                                         cudaMemcpyHostToDevice, st));
-        std::vector<int64_t> toff(nu + 1);
-        Q3A_TRY(pcm_core(fe, e, e->stage_in.as<float>(), poff.data(), n_samples + u0, nu, mode, e->stage_out.as<float>(),
-                         toff.data(), st));
-        for (int i = 0; i < nu; ++i) {
-            const int64_t rows = toff[i + 1] - toff[i];
-            if (n_tokens) n_tokens[u0 + i] = (int)rows;
-            if (rows > 0)
-                Q3A_CUDA(cudaMemcpyAsync(out[u0 + i], e->stage_out.as<float>() + toff[i] * width,
-                                         sizeof(float) * rows * width, cudaMemcpyDeviceToHost, st));
-        }
-        Q3A_CUDA(cudaStreamSynchronize(st));
-    }
-    return prof_collect(e, st);
+    Q3A_TRY(run_host_passes(e, pcm, n_samples, nf.data(), n_clips, mode, width, out, n_tokens,
+                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, int64_t* toff) {
+                                return pcm_core(fe, e, in_dev, in_off, n_samples + u0, nu, mode, out_dev, toff, e->stream);
+                            }));
+    return prof_collect(e, e->stream);
 }
 
 // Longest-processing-time-first assignment.  Cost model: per token ~0.71 GFLOP of dense work plus the

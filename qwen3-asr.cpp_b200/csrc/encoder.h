@@ -11,7 +11,11 @@ struct q3a_encoder {
     int device = 0;
     int fmt = q3a::OP_BF16;          // 16-bit operand type of every tensor-core kernel
     q3a_hparams hp{};
-    cudaStream_t stream = nullptr;   // used by the host-pointer entry points
+    cudaStream_t stream = nullptr;   // compute stream of the host-pointer entry points
+    // host-pointer entry points run as a 3-stage pipeline over passes: upload (copy_in) | compute (stream) |
+    // download (copy_out), staging buffers double-buffered by pass parity
+    cudaStream_t copy_in = nullptr, copy_out = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
 
     // ---- weights (one arena) -----------------------------------------------------------------
     q3a::DevBuf arena;
@@ -30,7 +34,7 @@ struct q3a_encoder {
     int pe_rows = 0;
 
     // ---- workspace (grows, never shrinks) -----------------------------------------------------
-    q3a::DevBuf planes1, planes2, feat, x, h, qkv, att, up, tables, stage_in, stage_out, stage_mel, stage_max;
+    q3a::DevBuf planes1, planes2, feat, x, h, qkv, att, up, tables, stage_in, stage_out, stage_in2, stage_out2, stage_mel, stage_max;
     int rcap1 = 0, rcap2 = 0, sigP2 = 0, sigP3 = 0;   // plane layout the zero rows were prepared for
     q3a::PinnedRing ring;
 

@@ -3,19 +3,22 @@
 // clamp(max-8) and (x+4)/4 scale.  Replaces log_mel_spectrogram (reference mel_spectrogram.cpp:484-628,
 // whose non-Apple path is a double-precision O(N^2) DFT, :569-600) and generate_mel_filters (:361-415).
 //
-// Kernel 1 (mel_frames_kernel): one CTA = one tile of 32 consecutive frames of one clip.
+// Kernel 1 (mel_frames_kernel): one CTA = one tile of 32 consecutive frames of one clip, 288 threads.
 //   load     5360 padded samples -> smem (float4, coalesced; reflect/zero rule of :499-515 at the edges)
-//   stage 1  800 tasks (frame, n1): 16 windowed samples -> rdft16 -> twiddle -> smem z[frame][k2][n1]
-//   stage 2  288 tasks (frame, k2): 25 complex -> dft25 -> |X|^2 -> smem power[frame][201]
-//   stage 3  4096 outputs (mel, frame): compressed filterbank row . power -> log10(max(.,1e-10))
-//            -> global [mel][frame] (a warp writes 32 consecutive frames of one mel row) and the
-//            running per-clip maximum over frames < n_len (:604-613) via one atomicMax per CTA.
+//   stage 1  thread = (frame mod 11, n1): window and W400 twiddles of its n1 live in registers for its
+//            three frames; 16 windowed samples -> rdft16 -> twiddle -> smem z[frame][k2][n1]
+//   stage 2  warp = k2, lane = frame: 25 complex -> dft25 -> |X|^2 -> smem power[bin][frame]
+//            (frame fastest, so stage 3 reads four frames of one bin with one LDS.128)
+//   stage 3  thread = (mel row, 4 frames): compressed filterbank row . power -> log10(max(.,1e-10))
+//            -> global [mel][frame] as float4, and the running per-clip maximum over frames < n_len
+//            (:604-613) via one atomicMax per CTA.
 // Kernel 2 (mel_finalize_kernel): x = (max(x, clipmax-8)+4)/4 in place (:615-625), float4.
 // Algorithmic HBM bytes per clip: 4*n_samples (PCM read once) + 4*n_mel*n_len (mel written once).
 #include "mel.h"
 #include "mel_fft.cuh"
 
 #include <cmath>
+#include <cstdint>
 #include <cstring>
 #include <vector>
 
@@ -30,12 +33,14 @@ constexpr int kMelThreads = 288;                         // 9 warps: 288 = 9 k2 
 constexpr int kTileSamples = (kFT - 1) * kHop + kNFft;   // 5360
 constexpr int kUnionFloats = kFT * kBins;                // 6432 >= kTileSamples
 static_assert(kUnionFloats >= kTileSamples, "power buffer aliases the sample buffer");
+constexpr int kS1Frames = 11;                            // frames stage 1 covers per sweep (11 * 25 = 275 threads)
+constexpr int kMaxTabWeights = 512, kMaxTabRows = 128;   // filterbank tables staged in smem up to this size
 
 struct MelSmem {
-    float u[kUnionFloats];            // samples (load, stage 1) then power[frame][201] (stage 2, 3)
+    float u[kUnionFloats];            // samples (load, stage 1) then power[bin][frame] (stage 2, 3)
     float2 z[kFT][9][25];             // stage-1 output
-    float hann[kNFft];
-    float2 tw[25 * 9];
+    float w[kMaxTabWeights];          // compressed filterbank rows
+    int bin0[kMaxTabRows], ptr[kMaxTabRows + 1];
     float red[16];
 };
 
@@ -79,8 +84,17 @@ mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restr
     const int n_valid = min(kFT, cd.n_len - f0);         // frames of this tile that exist
     const float* __restrict__ pcm = pcm_base + cd.pcm_off;
 
-    for (int i = tid; i < kNFft; i += kMelThreads) s.hann[i] = __ldg(g_hann + i);
-    for (int i = tid; i < 25 * 9; i += kMelThreads) s.tw[i] = __ldg(g_tw + i);
+    // filterbank tables: smem when they fit (the standard 128 x 201 bank has 396 non-zeros), else global
+    const bool tab_smem = n_mel <= kMaxTabRows && __ldg(row_ptr + n_mel) <= kMaxTabWeights;
+    if (tab_smem) {
+        const int nw = __ldg(row_ptr + n_mel);
+        for (int i = tid; i < nw; i += kMelThreads) s.w[i] = __ldg(weights + i);
+        for (int i = tid; i < n_mel; i += kMelThreads) s.bin0[i] = __ldg(row_bin0 + i);
+        for (int i = tid; i <= n_mel; i += kMelThreads) s.ptr[i] = __ldg(row_ptr + i);
+    }
+    const float* wtab = tab_smem ? s.w : weights;
+    const int* b0tab = tab_smem ? s.bin0 : row_bin0;
+    const int* ptab = tab_smem ? s.ptr : row_ptr;
 
     // ---- load the tile's samples -------------------------------------------------------------
     const int p0 = f0 * kHop;                             // first padded position of the tile
@@ -93,62 +107,98 @@ mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restr
         for (int i = tid; i < kTileSamples; i += kMelThreads)
             s.u[i] = (i < need) ? padded_sample(pcm, n, p0 + i) : 0.0f;
     }
-    __syncthreads();
 
     // ---- stage 1: 25 real 16-point DFTs per frame + twiddle -----------------------------------
-    for (int task = tid; task < kFT * 25; task += kMelThreads) {
-        const int f = task / 25, n1 = task - f * 25;
-        if (f < n_valid) {
-            float x[16];
-            const float* xs = s.u + f * kHop + n1;
+    // (window and twiddles are fetched while the sample loads are in flight)
+    {
+        const bool s1 = tid < kS1Frames * 25;
+        const int fi = tid / 25, n1 = tid - fi * 25;
+        float hw[16];
+        float2 tw[9];
+        if (s1) {
 #pragma unroll
-            for (int n2 = 0; n2 < 16; ++n2) x[n2] = xs[25 * n2] * s.hann[n1 + 25 * n2];
-            fft::cpx y[9];
-            fft::rdft16(x, y);
+            for (int n2 = 0; n2 < 16; ++n2) hw[n2] = __ldg(g_hann + n1 + 25 * n2);
 #pragma unroll
-            for (int k2 = 0; k2 < 9; ++k2) {
-                float2 w = s.tw[n1 * 9 + k2];
-                fft::cpx zz = fft::cmul(y[k2], fft::mk(w.x, w.y));
-                s.z[f][k2][n1] = make_float2(zz.re, zz.im);
+            for (int k2 = 1; k2 < 9; ++k2) tw[k2] = __ldg(g_tw + n1 * 9 + k2);
+        }
+        __syncthreads();
+        if (s1) {
+#pragma unroll 1
+            for (int f = fi; f < n_valid; f += kS1Frames) {
+                float x[16];
+                const float* xs = s.u + f * kHop + n1;
+#pragma unroll
+                for (int n2 = 0; n2 < 16; ++n2) x[n2] = xs[25 * n2] * hw[n2];
+                fft::cpx y[9];
+                fft::rdft16(x, y);
+                s.z[f][0][n1] = make_float2(y[0].re, y[0].im);      // W400^0 = 1
+#pragma unroll
+                for (int k2 = 1; k2 < 9; ++k2) {
+                    fft::cpx zz = fft::cmul(y[k2], fft::mk(tw[k2].x, tw[k2].y));
+                    s.z[f][k2][n1] = make_float2(zz.re, zz.im);
+                }
             }
         }
     }
     __syncthreads();
 
-    // ---- stage 2: 9 complex 25-point DFTs per frame -> power spectrum --------------------------
+    // ---- stage 2: 9 complex 25-point DFTs per frame -> power spectrum, stored [bin][frame] -------
     {
-        const int f = tid / 9, k2 = tid - f * 9;          // 288 tasks, one per thread
+        const int f = tid & 31, k2 = tid >> 5;            // warp = k2, lane = frame: both smem sides conflict-free
         if (f < n_valid) {
             fft::cpx a[25];
 #pragma unroll
             for (int i = 0; i < 25; ++i) { float2 v = s.z[f][k2][i]; a[i] = fft::mk(v.x, v.y); }
             fft::dft25(a);
-            float* pw = s.u + f * kBins;
-            const bool mirror_ok = (k2 != 0) && (k2 != 8);
+            // bin k = k2 + 16 k1 is direct for k1 <= 12 (k <= 200) and the mirror 400-k otherwise.  Mirrors go
+            // first: for k2 = 0 and 8 they land on bins this same thread also computes directly, and the
+            // direct value must win (program order within the thread); for other k2 they are unique.
+            float* pw = s.u + f;
 #pragma unroll
-            for (int k1 = 0; k1 < 25; ++k1) {
-                const int k = k2 + 16 * k1;
-                const float p = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
-                if (k <= 200) pw[k] = p;
-                else if (mirror_ok) pw[400 - k] = p;
-            }
+            for (int k1 = 13; k1 < 25; ++k1)
+                pw[(400 - 16 * k1 - k2) * kFT] = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
+#pragma unroll
+            for (int k1 = 0; k1 < 13; ++k1)
+                pw[(16 * k1 + k2) * kFT] = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
         }
     }
     __syncthreads();
 
     // ---- stage 3: filterbank, log10, store, running max ----------------------------------------
     float vmax = -INFINITY;
-    const int f = tid & 31;
-    float* __restrict__ out = mel_base + cd.mel_off;
-    for (int m = tid >> 5; m < n_mel; m += kMelThreads / 32) {
-        const int b0 = __ldg(row_bin0 + m), w0 = __ldg(row_ptr + m), w1 = __ldg(row_ptr + m + 1);
-        if (f < n_valid) {
-            const float* pw = s.u + f * kBins + b0;
-            float acc = 0.0f;
-            for (int j = w0; j < w1; ++j) acc = fmaf(__ldg(weights + j), pw[j - w0], acc);
-            const float v = log10f(fmaxf(acc, 1e-10f));
-            out[(long long)m * cd.n_len + f0 + f] = v;
-            vmax = fmaxf(vmax, v);
+    {
+        const int q = tid & 7;                            // frames 4q .. 4q+3 of the tile
+        float* __restrict__ out = mel_base + cd.mel_off;
+        const bool vec_ok = ((cd.n_len & 3) | (int)(reinterpret_cast<uintptr_t>(out) & 15)) == 0;   // rows stay 16-byte aligned
+        const float4* pw4 = reinterpret_cast<const float4*>(s.u) + q;
+        if (4 * q < n_valid) {
+            for (int m = tid >> 3; m < n_mel; m += kMelThreads / 8) {
+                const int b0 = b0tab[m], w0 = ptab[m], w1 = ptab[m + 1];
+                float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                const float4* pp = pw4 + b0 * (kFT / 4);
+#pragma unroll 4
+                for (int j = w0; j < w1; ++j) {
+                    const float w = wtab[j];
+                    const float4 p = pp[(j - w0) * (kFT / 4)];
+                    acc.x = fmaf(w, p.x, acc.x); acc.y = fmaf(w, p.y, acc.y);
+                    acc.z = fmaf(w, p.z, acc.z); acc.w = fmaf(w, p.w, acc.w);
+                }
+                const float kLog10Of2 = 0.30102999566398120f;
+                float4 v;
+                v.x = __log2f(fmaxf(acc.x, 1e-10f)) * kLog10Of2; v.y = __log2f(fmaxf(acc.y, 1e-10f)) * kLog10Of2;
+                v.z = __log2f(fmaxf(acc.z, 1e-10f)) * kLog10Of2; v.w = __log2f(fmaxf(acc.w, 1e-10f)) * kLog10Of2;
+                float* dst = out + (long long)m * cd.n_len + f0 + 4 * q;
+                const int left = n_valid - 4 * q;         // >= 1
+                if (left >= 4 && vec_ok) {
+                    *reinterpret_cast<float4*>(dst) = v;
+                    vmax = fmaxf(vmax, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+                } else {
+                    dst[0] = v.x; vmax = fmaxf(vmax, v.x);
+                    if (left > 1) { dst[1] = v.y; vmax = fmaxf(vmax, v.y); }
+                    if (left > 2) { dst[2] = v.z; vmax = fmaxf(vmax, v.z); }
+                    if (left > 3) { dst[3] = v.w; vmax = fmaxf(vmax, v.w); }
+                }
+            }
         }
     }
 #pragma unroll

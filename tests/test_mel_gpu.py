@@ -120,5 +120,11 @@ def test_device_resident_and_unfinalized(fe, filters):
     for i, c in enumerate(clips):
         raw = MO.log_mel_raw_numpy(c, filters)[:, :len(c) // 160]
         got = mel[moffs[i]:moffs[i] + raw.size].cpu().numpy().reshape(raw.shape)
-        assert np.abs(got - raw).max() <= 4e-4                      # raw log10 values are 4x the final scale
+        # raw log10 values are 4x the final scale.  Every consumer clamps at (clip max - 8) first (the fused
+        # path does it inside conv1's loads, mel_spectrogram.cpp:615-625), so the 1e-4 bound of the final
+        # scale applies after that clamp; cells below it sit at the fp32 noise floor of the FFT (relative
+        # to the frame's strongest bin) and only get a sanity bound.
+        floor = raw.max() - 8.0
+        assert np.abs(np.maximum(got, floor) - np.maximum(raw, floor)).max() <= 4e-4
+        assert np.abs(got - raw).max() <= 5e-3
         assert abs(float(mx[i]) - raw.max()) <= 4e-4
