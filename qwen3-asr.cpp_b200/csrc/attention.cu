@@ -84,11 +84,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
     if (warp == 0) {
         // barriers, first loads, then the TMEM allocation: the fetch latency runs under it
         if (tc::elect_one()) {
+            pdl_trigger();
             tc::prefetch_tmap(&tmap_qkv);
             tc::mbar_init(bar_q, 1); tc::mbar_init(bar_s, 1); tc::mbar_init(bar_o, 1);
             tc::mbar_init(bar_k(0), 1); tc::mbar_init(bar_k(1), 1);
             tc::mbar_init(bar_v(0), 1); tc::mbar_init(bar_v(1), 1);
             tc::fence_barrier_init();
+            pdl_wait();                                    // qkv is the previous kernel's output
             tc::mbar_arrive_expect_tx(bar_q, kTileBytes);
             tc::tma_load_2d(sQ, &tmap_qkv, bar_q, col_q, t.q0);
             tc::mbar_arrive_expect_tx(bar_k(0), kTileBytes);
@@ -107,6 +109,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
     __syncthreads();
     tc::fence_after_sync();
     tmem = *tmem_slot_ptr;
+    pdl_wait();
     const uint32_t t_row = tmem + ((uint32_t)(warp * 32) << 16);   // this warp's TMEM lane quadrant
     if (warp == 0) {
         tc::mbar_wait(bar_q, 0);
@@ -331,9 +334,9 @@ int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnT
     }
     dim3 grid(n_tiles, n_heads);
     if (fmt == OP_F16)
-        attention_kernel<__half><<<grid, 128, kAttnSmem, stream>>>(tm, tiles_dev, (__half*)out, d);
+        Q3A_CUDA(launch_pdl(attention_kernel<__half>, grid, dim3(128), kAttnSmem, stream, tm, tiles_dev, (__half*)out, d));
     else
-        attention_kernel<__nv_bfloat16><<<grid, 128, kAttnSmem, stream>>>(tm, tiles_dev, (__nv_bfloat16*)out, d);
+        Q3A_CUDA(launch_pdl(attention_kernel<__nv_bfloat16>, grid, dim3(128), kAttnSmem, stream, tm, tiles_dev, (__nv_bfloat16*)out, d));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;

@@ -1,5 +1,6 @@
 // Shared host/device helpers for libq3a (B200 / sm_100a only).
 #pragma once
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -133,6 +134,29 @@ struct PinnedRing {
         }
     }
 };
+
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------
+// Every kernel of the path is launched with programmatic stream serialization: its CTAs may become resident
+// while the previous kernel of the stream is still draining, run their prologue (barrier init, TMEM
+// allocation, descriptor prefetch) and then block in pdl_wait() until the previous grid has completed and
+// its writes are visible.  pdl_trigger() lets the next kernel do the same with respect to this one.  A kernel
+// must not touch global memory another kernel of the stream writes, nor write global memory, before pdl_wait().
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    static const bool off = getenv("Q3A_NO_PDL") != nullptr;      // debugging aid: plain stream order
+    cfg.attrs = at; cfg.numAttrs = off ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
 
 // make `device` current and check that it is an sm_100 part (there is no other code path)
 int use_device(int device);

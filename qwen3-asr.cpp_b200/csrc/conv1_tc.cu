@@ -72,7 +72,8 @@ conv1_tc_kernel(const float* __restrict__ mel, const StemChunk* __restrict__ chu
     const int N0 = C < 256 ? C : 256, N1 = C - N0;
     const int n_halves = N1 > 0 ? 2 : 1;
 
-    // one-time: weight image and bias into smem, barriers, TMEM
+    // one-time: weight image and bias into smem, barriers, TMEM (weights are constants: legal before pdl_wait)
+    pdl_trigger();
     for (int i = tid; i < C * 8; i += kC1Threads) reinterpret_cast<uint4*>(gen)[i] = __ldg(w_image + i);
     for (int i = tid; i < C; i += kC1Threads) gBias[i] = __ldg(bias + i);
     if (tid == 0) {
@@ -87,6 +88,7 @@ conv1_tc_kernel(const float* __restrict__ mel, const StemChunk* __restrict__ chu
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *tmem_slot_ptr;
+    pdl_wait();
 
     if (warp < 4) {
         // ===================== A-tile producers =====================
@@ -280,8 +282,8 @@ int conv1_tc_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks,
     int sms = 148;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const int grid = n_tiles < sms ? n_tiles : sms;
-    kern<<<grid, kC1Threads, smem, stream>>>(mel, chunks_dev, n_tiles, tpc, P2, clip_max,
-                                             reinterpret_cast<const uint4*>(w_image), bias, C, tm, rows_per_plane);
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kC1Threads), smem, stream, mel, chunks_dev, n_tiles, tpc, P2, clip_max,
+                        reinterpret_cast<const uint4*>(w_image), bias, C, tm, rows_per_plane));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;

@@ -69,7 +69,7 @@ static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t strea
     LoaderLinear loader{ceil_div(a.K, kBlockK)};
     const int tiles = ceil_div(a.M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
     const int grid = 2 * (tiles < pairs ? tiles : pairs);
-    kern<<<grid, kGemmThreads, S::kTotal, stream>>>(ta, tb, tc_, a.M, a.N, loader, epi);
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, tc_, a.M, a.N, loader, epi));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;

@@ -152,6 +152,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     const int num_tiles = m_blocks * n_blocks;
     const int num_kb = loader.num_k_blocks;
 
+    pdl_trigger();
     if (warp == 0 && lane == 0) {
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
@@ -169,6 +170,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     tc::cluster_sync();                       // barriers of both CTAs initialised before any remote signal
     tc::fence_after_sync();
     const uint32_t tmem_base = *tmem_slot_ptr;
+    pdl_wait();                               // everything above overlapped the previous kernel's tail
 
     if (warp == 0) {
         // ===================== TMA producer (both CTAs; converged warp, one elected lane issues) ==========

@@ -70,6 +70,8 @@ mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restr
     extern __shared__ __align__(16) unsigned char smem_raw[];
     MelSmem& s = *reinterpret_cast<MelSmem*>(smem_raw);
     const int tid = threadIdx.x;
+    pdl_trigger();
+    pdl_wait();
 
     // which clip does this tile belong to?  (tile0 is ascending; n_clips is small)
     int lo = 0, hi = n_clips - 1;
@@ -305,9 +307,10 @@ int mel_launch(q3a_frontend* fe, const float* pcm_dev, const int64_t* pcm_off, c
     const MelClipDesc* d_desc = fe->desc.as<MelClipDesc>();
     unsigned* d_max = fe->maxbuf.as<unsigned>();
     if (tiles > 0) {
-        mel_frames_kernel<<<tiles, kMelThreads, sizeof(MelSmem), stream>>>(
-            pcm_dev, d_desc, n_clips, fe->d_hann, fe->d_twiddle, fe->d_row_bin0, fe->d_row_ptr, fe->d_weights,
-            fe->n_mel, mel_dev, d_max);
+        Q3A_CUDA(launch_pdl(mel_frames_kernel, dim3(tiles), dim3(kMelThreads), sizeof(MelSmem), stream,
+                            pcm_dev, d_desc, n_clips, (const float*)fe->d_hann, (const float2*)fe->d_twiddle,
+                            (const int*)fe->d_row_bin0, (const int*)fe->d_row_ptr, (const float*)fe->d_weights, fe->n_mel,
+                            mel_dev, d_max));
         ++g_launch_counter;
         Q3A_CUDA(cudaGetLastError());
     }

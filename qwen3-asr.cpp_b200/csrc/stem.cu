@@ -15,6 +15,8 @@ conv1_kernel(const float* __restrict__ mel, const StemChunk* __restrict__ chunks
              const float* __restrict__ clip_max, const float* __restrict__ w, const float* __restrict__ bias, int C,
              OpT* __restrict__ planes, long long plane_stride) {
     __shared__ float patch[3][kMelRows + 2];          // [dt][f + 1], f = -1 .. 128
+    pdl_trigger();
+    pdl_wait();
     const StemChunk ck = chunks[blockIdx.x];
     const int t1 = blockIdx.y;
     const int groups = C >> 3;
@@ -88,7 +90,7 @@ int conv1_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks, in
     const int ppi = 256 / groups;
     const int threads = ((groups * ppi + 31) / 32) * 32;
     dim3 grid(n_chunks, 2 * (P2 - 1));
-    conv1_kernel<OpT><<<grid, threads, 0, stream>>>(mel, chunks_dev, P2, clip_max, w, bias, C, planes, plane_stride);
+    Q3A_CUDA(launch_pdl(conv1_kernel<OpT>, grid, dim3(threads), 0, stream, mel, chunks_dev, P2, clip_max, w, bias, C, planes, plane_stride));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;
@@ -101,6 +103,8 @@ template <class OpT>
 __global__ void __launch_bounds__(256)
 layernorm_kernel(const float* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                  float eps, int T, int d, OpT* __restrict__ out) {
+    pdl_trigger();
+    pdl_wait();
     const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (row >= T) return;
     const int lane = threadIdx.x & 31;
@@ -148,7 +152,7 @@ int layernorm_launch(const float* x, const float* gamma, const float* beta, floa
                      cudaStream_t stream) {
     if (T == 0) return Q3A_OK;
     if (d % 4 || d > 1024) { set_error("layernorm: d_model must be a multiple of 4, at most 1024"); return Q3A_ERR_ARG; }
-    layernorm_kernel<OpT><<<ceil_div(T, 8), 256, 0, stream>>>(x, gamma, beta, eps, T, d, out);
+    Q3A_CUDA(launch_pdl(layernorm_kernel<OpT>, dim3(ceil_div(T, 8)), dim3(256), 0, stream, x, gamma, beta, eps, T, d, out));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;
