@@ -13,6 +13,7 @@ struct AttnTile {
 
 // one tile per 128 queries of every segment; cu_seqlens has n_seg+1 ascending entries
 void attention_tiles(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& tiles);
+inline int attention_tile_count(int seg_len) { return (seg_len + 127) / 128; }   // tiles attention_tiles() emits per segment
 // 4 * head_dim * H * sum(len^2): QK^T and PV, 2 flops per MAC, no padding counted
 double attention_flops(const int* cu_seqlens, int n_seg, int n_heads);
 // qkv: [T][3*H*64] 16-bit (q | k | v column blocks), out: [T][H*64] 16-bit

@@ -261,12 +261,15 @@ void conv1_tc_weight_image(const float* w /*[C][9]*/, int C, std::vector<uint8_t
 
 template <class OpT>
 int conv1_tc_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks, int P2, const float* clip_max,
-                    const void* w_image, const float* bias, int C, OpT* planes, int R_cap, cudaStream_t stream) {
+                    const void* w_image, const float* bias, int C, OpT* planes, int R_cap, int row0, cudaStream_t stream) {
     if (n_chunks == 0) return Q3A_OK;
     if (!conv1_tc_supported(C)) { set_error("conv1_tc: unsupported channel count"); return Q3A_ERR_ARG; }
+    // `chunks_dev` may be a sub-range of the pass's chunks: its first chunk owns plane rows from row0 on, so the
+    // map starts there (plane stride unchanged) and stops at the end of the arena
     const int rows_per_plane = R_cap * 32;
     CUtensorMap tm;
-    Q3A_TRY(make_tmap_tile32(&tm, planes, 2, (uint64_t)4 * rows_per_plane, (uint64_t)C, (uint64_t)C));
+    Q3A_TRY(make_tmap_tile32(&tm, planes + (size_t)row0 * 32 * C, 2, (uint64_t)4 * rows_per_plane - (uint64_t)row0 * 32,
+                             (uint64_t)C, (uint64_t)C));
     auto kern = conv1_tc_kernel<OpT>;
     const int smem = c1_smem_bytes(C);
     static bool attr_done[64] = {false};
@@ -290,8 +293,8 @@ int conv1_tc_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks,
 }
 
 template int conv1_tc_launch<__nv_bfloat16>(const float*, const StemChunk*, int, int, const float*, const void*,
-                                            const float*, int, __nv_bfloat16*, int, cudaStream_t);
+                                            const float*, int, __nv_bfloat16*, int, int, cudaStream_t);
 template int conv1_tc_launch<__half>(const float*, const StemChunk*, int, int, const float*, const void*, const float*,
-                                     int, __half*, int, cudaStream_t);
+                                     int, __half*, int, int, cudaStream_t);
 
 }  // namespace q3a

@@ -13,9 +13,12 @@
 #include "mel.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <numeric>
 
 namespace q3a {
@@ -133,10 +136,23 @@ static int prof_collect(q3a_encoder* e, cudaStream_t st) {
 }
 
 // ---- the forward pass --------------------------------------------------------------------------------
+// Optional partition of one forward pass, used by the host-pointer entry points to overlap PCIe copies with
+// kernels.  Inputs: the stem runs part by part (utterances [in_split[i], in_split[i+1])), calling before_stem
+// first -- the hook makes the part's input resident (waits for its upload, runs its mel kernels).  Outputs: the
+// last `tail_layers` layers and the projection run part by part over [out_split[i], out_split[i+1]), calling
+// after_out when a part's rows are final, so its download overlaps the next part's tail.  Utterances are
+// independent end to end and the kernels are batch-invariant, so the partition never changes a result.
+struct PartHooks {
+    std::vector<int> in_split, out_split;
+    std::function<int(int part, int u0, int u1)> before_stem;
+    std::function<int(int part, int u0, int u1, const int64_t* tok_off)> after_out;
+    int tail_layers = 3;
+};
+
 template <class OpT>
 static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_off, const float* max_dev,
                        const int* n_frames, int n_utts, int mode, float* out_dev, int64_t* tok_off_out,
-                       cudaStream_t st) {
+                       cudaStream_t st, const PartHooks* hk) {
     const q3a_hparams& hp = e->hp;
     const int d = hp.d_model, C = hp.conv_channels, H = hp.n_attention_heads, ffn = hp.ffn_dim;
     const int fmt = e->fmt;
@@ -148,10 +164,13 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     std::vector<StemChunk> chunks;
     std::vector<int> t2_valid, n_tok, tok_base, pos, cu;
     std::vector<int64_t> tok_off(n_utts + 1, 0);
+    std::vector<int> utt_chunk0(n_utts + 1, 0), utt_seg0(n_utts + 1, 0);
     int T = 0, max_len = 0, max_pos = 0;
     cu.push_back(0);
     for (int u = 0; u < n_utts; ++u) {
         tok_off[u] = T;
+        utt_chunk0[u] = (int)chunks.size();
+        utt_seg0[u] = (int)cu.size() - 1;
         const int nf = n_frames[u];
         if (nf < 0) { set_error("encode: negative n_frames"); return Q3A_ERR_ARG; }
         const int step = chunked ? kChunkFrames : std::max(nf, 1);
@@ -179,12 +198,27 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         }
     }
     tok_off[n_utts] = T;
+    utt_chunk0[n_utts] = (int)chunks.size();
+    utt_seg0[n_utts] = (int)cu.size() - 1;
     if (tok_off_out) std::memcpy(tok_off_out, tok_off.data(), sizeof(int64_t) * (n_utts + 1));
     const int n_chunks = (int)chunks.size();
-    if (T == 0) return Q3A_OK;
+    // partition (one part each way without hooks); a part that is empty still gets its hook calls
+    std::vector<int> in_split = hk && hk->in_split.size() >= 2 ? hk->in_split : std::vector<int>{0, n_utts};
+    std::vector<int> out_split = hk && hk->out_split.size() >= 2 ? hk->out_split : std::vector<int>{0, n_utts};
+    if (T == 0) {
+        if (hk && hk->before_stem)
+            for (size_t i = 0; i + 1 < in_split.size(); ++i) Q3A_TRY(hk->before_stem((int)i, in_split[i], in_split[i + 1]));
+        if (hk && hk->after_out)
+            for (size_t i = 0; i + 1 < out_split.size(); ++i) Q3A_TRY(hk->after_out((int)i, out_split[i], out_split[i + 1], tok_off.data()));
+        return Q3A_OK;
+    }
     const int n_seg = (int)cu.size() - 1;
     std::vector<AttnTile> tiles;
-    if (mode != Q3A_MODE_CONV_ONLY) attention_tiles(cu.data(), n_seg, tiles);
+    std::vector<int> seg_tile0(n_seg + 1, 0);             // first attention tile of every segment
+    if (mode != Q3A_MODE_CONV_ONLY) {
+        attention_tiles(cu.data(), n_seg, tiles);
+        for (int sgi = 0; sgi < n_seg; ++sgi) seg_tile0[sgi + 1] = seg_tile0[sgi] + attention_tile_count(cu[sgi + 1] - cu[sgi]);
+    }
 
     const int maxL1 = (max_len - 1) / 2 + 1;
     const int P2 = 1 + (maxL1 + 1) / 2;           // rows per chunk of conv2's input planes / output row space
@@ -250,96 +284,143 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     OpT* planes2 = e->planes2.as<OpT>();
     const long long ps1 = (long long)e->rcap1 * F2 * C, ps2 = (long long)e->rcap2 * F3 * C;
 
-    // ---- stem -------------------------------------------------------------------------------------------------
-    const int sp_stem = prof.begin(SP_STEM);
-    {
-        const int sp = prof.begin(SP_OTHER);
-        if (e->conv1_wimg)
-            Q3A_TRY(conv1_tc_launch<OpT>(mel_dev, d_chunks, n_chunks, P2, max_dev, e->conv1_wimg, e->conv1_b, C, planes1,
-                                         e->rcap1, st));
-        else
-            Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks, n_chunks, P2, max_dev, e->conv1_w, e->conv1_b, C, planes1, ps1, st));
-        prof.end(sp);
-    }
-    {
-        ConvArgs a;
-        a.planes = planes1; a.R_cap = e->rcap1; a.R_used = r1; a.Fh = F2; a.C = C;
-        a.w = e->conv2_w; a.N = C; a.bias = e->conv2_b; a.P = P2;
-        a.out_planes = planes2; a.P_next = P3; a.out_plane_stride = ps2; a.ot_valid = d_t2;
-        const int sp = prof.begin(SP_GEMM);
-        Q3A_TRY(gemm_conv(false, fmt, a, st));
-        prof.end(sp);
-        double m = 0; for (int c = 0; c < n_chunks; ++c) m += (double)t2_valid[c] * F2;
-        e->tm.gemm_flops += 2.0 * m * C * 9.0 * C; ++e->tm.gemm_launches;
-    }
-    {
-        ConvArgs a;
-        a.planes = planes2; a.R_cap = e->rcap2; a.R_used = r2; a.Fh = F3; a.C = C;
-        a.w = e->conv3_w; a.N = C; a.bias = e->conv3_b; a.P = P3;
-        a.feat = e->feat.p; a.n_tok = d_ntok; a.tok_base = d_base;
-        const int sp = prof.begin(SP_GEMM);
-        Q3A_TRY(gemm_conv(true, fmt, a, st));
-        prof.end(sp);
-        e->tm.gemm_flops += 2.0 * (double)T * F3 * C * 9.0 * C; ++e->tm.gemm_launches;
-    }
+    // ---- stem, part by part ---------------------------------------------------------------------------------
     auto linear = [&](EpiKind kind, const void* A, int K, const void* W, int N, void* out, const float* bias,
-                      const float* res, const float* pe_tab, const int* pos_tab) -> int {
+                      const float* res, const float* pe_tab, const int* pos_tab, int rows) -> int {
+        if (rows <= 0) return Q3A_OK;
         LinearArgs a;
-        a.a = A; a.M = T; a.K = K; a.lda = K; a.w = W; a.N = N; a.ldw = K; a.out = out; a.ldc = N;
+        a.a = A; a.M = rows; a.K = K; a.lda = K; a.w = W; a.N = N; a.ldw = K; a.out = out; a.ldc = N;
         a.bias = bias; a.res = res; a.pe = pe_tab; a.pos = pos_tab;
         const int sp = prof.begin(SP_GEMM);
         const int rc = gemm_linear(kind, fmt, a, st);
         prof.end(sp);
-        e->tm.gemm_flops += 2.0 * (double)T * N * K; ++e->tm.gemm_launches;
+        e->tm.gemm_flops += 2.0 * (double)rows * N * K; ++e->tm.gemm_launches;
         return rc;
     };
+    auto rows16 = [](void* p, size_t cols, int t0) { return (void*)(static_cast<uint16_t*>(p) + (size_t)t0 * cols); };
+    float* x = e->x.as<float>();
+    float* stem_out = mode == Q3A_MODE_CONV_ONLY ? out_dev : x;
+    const int sp_stem = prof.begin(SP_STEM);
+    for (size_t part = 0; part + 1 < in_split.size(); ++part) {
+        const int ua = in_split[part], ub = in_split[part + 1];
+        if (hk && hk->before_stem) Q3A_TRY(hk->before_stem((int)part, ua, ub));
+        const int c0 = utt_chunk0[ua], nc = utt_chunk0[ub] - c0;
+        const int t0 = (int)tok_off[ua], tn = (int)(tok_off[ub] - tok_off[ua]);
+        if (nc == 0) continue;
+        const int row1 = c0 * P2, row2 = c0 * P3;          // first plane rows of the part
+        {
+            const int sp = prof.begin(SP_OTHER);
+            if (e->conv1_wimg)
+                Q3A_TRY(conv1_tc_launch<OpT>(mel_dev, d_chunks + c0, nc, P2, max_dev, e->conv1_wimg, e->conv1_b, C, planes1,
+                                             e->rcap1, row1, st));
+            else
+                Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks + c0, nc, P2, max_dev, e->conv1_w, e->conv1_b, C,
+                                          planes1 + (size_t)row1 * F2 * C, ps1, st));
+            prof.end(sp);
+        }
+        {
+            ConvArgs a;
+            a.planes = planes1 + (size_t)row1 * F2 * C; a.R_cap = e->rcap1; a.R_map = e->rcap1 - row1; a.R_used = nc * P2;
+            a.Fh = F2; a.C = C;
+            a.w = e->conv2_w; a.N = C; a.bias = e->conv2_b; a.P = P2;
+            a.out_planes = planes2 + (size_t)row2 * F3 * C; a.P_next = P3; a.out_plane_stride = ps2; a.ot_valid = d_t2 + c0;
+            const int sp = prof.begin(SP_GEMM);
+            Q3A_TRY(gemm_conv(false, fmt, a, st));
+            prof.end(sp);
+            double m = 0; for (int c = c0; c < c0 + nc; ++c) m += (double)t2_valid[c] * F2;
+            e->tm.gemm_flops += 2.0 * m * C * 9.0 * C; ++e->tm.gemm_launches;
+        }
+        {
+            ConvArgs a;
+            a.planes = planes2 + (size_t)row2 * F3 * C; a.R_cap = e->rcap2; a.R_map = e->rcap2 - row2; a.R_used = nc * P3;
+            a.Fh = F3; a.C = C;
+            a.w = e->conv3_w; a.N = C; a.bias = e->conv3_b; a.P = P3;
+            a.feat = e->feat.p; a.n_tok = d_ntok + c0; a.tok_base = d_base + c0;
+            const int sp = prof.begin(SP_GEMM);
+            Q3A_TRY(gemm_conv(true, fmt, a, st));
+            prof.end(sp);
+            e->tm.gemm_flops += 2.0 * (double)tn * F3 * C * 9.0 * C; ++e->tm.gemm_launches;
+        }
+        if (mode == Q3A_MODE_CONV_ONLY)
+            Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
+                           nullptr, nullptr, nullptr, nullptr, tn));
+        else
+            Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
+                           nullptr, nullptr, e->pe.as<float>(), d_pos + t0, tn));
+    }
+    prof.end(sp_stem);
     if (mode == Q3A_MODE_CONV_ONLY) {
-        Q3A_TRY(linear(EPI_POSEMB_F32, e->feat.p, feat_dim, e->conv_out_w, d, out_dev, nullptr, nullptr, nullptr, nullptr));
-        prof.end(sp_stem);
+        if (hk && hk->after_out)
+            for (size_t i = 0; i + 1 < out_split.size(); ++i) Q3A_TRY(hk->after_out((int)i, out_split[i], out_split[i + 1], tok_off.data()));
         return Q3A_OK;
     }
-    float* x = e->x.as<float>();
-    Q3A_TRY(linear(EPI_POSEMB_F32, e->feat.p, feat_dim, e->conv_out_w, d, x, nullptr, nullptr, e->pe.as<float>(), d_pos));
-    prof.end(sp_stem);
 
-    // ---- transformer layers ---------------------------------------------------------------------------------
+    // ---- transformer layers: all but the tail over the whole pass, the tail + projection part by part ----------
     const int sp_x = prof.begin(SP_XFMR);
     OpT* h = e->h.as<OpT>();
-    auto ln = [&](const float* g, const float* b) -> int {
-        const int sp = prof.begin(SP_OTHER);
-        const int rc = layernorm_launch<OpT>(x, g, b, hp.layer_norm_eps, T, d, h, st);
-        prof.end(sp);
-        return rc;
-    };
-    const double attn_fl = attention_flops(cu.data(), n_seg, H);
-    for (const auto& L : e->layers) {
-        Q3A_TRY(ln(L.ln1_g, L.ln1_b));
-        Q3A_TRY(linear(EPI_BIAS_OP, h, d, L.w_qkv, 3 * d, e->qkv.p, L.b_qkv, nullptr, nullptr, nullptr));
-        {
-            const int sp = prof.begin(SP_ATTN);
-            Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles, (int)tiles.size(), fmt, st));
+    const double attn_fl_per_tile_unit = 4.0 * 64 * H;
+    auto run_layers = [&](int l0, int l1, int ua, int ub, bool post) -> int {
+        const int t0 = (int)tok_off[ua], tn = (int)(tok_off[ub] - tok_off[ua]);
+        if (tn <= 0) return Q3A_OK;
+        const int sg0 = utt_seg0[ua], sg1 = utt_seg0[ub];
+        const int tile0 = seg_tile0[sg0], n_tiles = seg_tile0[sg1] - tile0;
+        double attn_fl = 0.0;
+        for (int sgi = sg0; sgi < sg1; ++sgi) { const double len = cu[sgi + 1] - cu[sgi]; attn_fl += attn_fl_per_tile_unit * len * len; }
+        float* xr = x + (size_t)t0 * d;
+        void* hr = rows16(h, d, t0);
+        void* attr = rows16(e->att.p, d, t0);
+        void* upr = rows16(e->up.p, ffn, t0);
+        auto ln = [&](const float* g, const float* b) -> int {
+            const int sp = prof.begin(SP_OTHER);
+            const int rc = layernorm_launch<OpT>(xr, g, b, hp.layer_norm_eps, tn, d, static_cast<OpT*>(hr), st);
             prof.end(sp);
-            e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;
+            return rc;
+        };
+        for (int li = l0; li < l1; ++li) {
+            const auto& L = e->layers[li];
+            Q3A_TRY(ln(L.ln1_g, L.ln1_b));
+            Q3A_TRY(linear(EPI_BIAS_OP, hr, d, L.w_qkv, 3 * d, rows16(e->qkv.p, 3 * (size_t)d, t0), L.b_qkv, nullptr, nullptr, nullptr, tn));
+            {
+                const int sp = prof.begin(SP_ATTN);
+                Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
+                prof.end(sp);
+                e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;
+            }
+            Q3A_TRY(linear(EPI_BIAS_RES_F32, attr, d, L.w_o, d, xr, L.b_o, xr, nullptr, nullptr, tn));
+            Q3A_TRY(ln(L.ln2_g, L.ln2_b));
+            Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, L.w_up, ffn, upr, L.b_up, nullptr, nullptr, nullptr, tn));
+            Q3A_TRY(linear(EPI_BIAS_RES_F32, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn));
         }
-        Q3A_TRY(linear(EPI_BIAS_RES_F32, e->att.p, d, L.w_o, d, x, L.b_o, x, nullptr, nullptr));
-        Q3A_TRY(ln(L.ln2_g, L.ln2_b));
-        Q3A_TRY(linear(EPI_BIAS_GELU_OP, h, d, L.w_up, ffn, e->up.p, L.b_up, nullptr, nullptr, nullptr));
-        Q3A_TRY(linear(EPI_BIAS_RES_F32, e->up.p, ffn, L.w_down, d, x, L.b_down, x, nullptr, nullptr));
-    }
-    Q3A_TRY(ln(e->lnp_g, e->lnp_b));
-    Q3A_TRY(linear(EPI_BIAS_GELU_OP, h, d, e->w_p1, d, e->att.p, e->b_p1, nullptr, nullptr, nullptr));
-    Q3A_TRY(linear(EPI_BIAS_F32, e->att.p, d, e->w_p2, hp.out_dim, out_dev, e->b_p2, nullptr, nullptr, nullptr));
+        if (post) {
+            Q3A_TRY(ln(e->lnp_g, e->lnp_b));
+            Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, e->w_p1, d, attr, e->b_p1, nullptr, nullptr, nullptr, tn));
+            Q3A_TRY(linear(EPI_BIAS_F32, attr, d, e->w_p2, hp.out_dim, out_dev + (size_t)t0 * hp.out_dim, e->b_p2, nullptr, nullptr,
+                           nullptr, tn));
+        }
+        return Q3A_OK;
+    };
+    const int n_layers = (int)e->layers.size();
+    const int n_out = (int)out_split.size() - 1;
+    const int tail = n_out > 1 ? std::min(std::max(hk->tail_layers, 0), n_layers) : 0;
+    Q3A_TRY(run_layers(0, n_layers - tail, 0, n_utts, n_out <= 1));
+    if (n_out > 1)
+        for (int i = 0; i < n_out; ++i) {
+            Q3A_TRY(run_layers(n_layers - tail, n_layers, out_split[i], out_split[i + 1], true));
+            if (hk->after_out) Q3A_TRY(hk->after_out(i, out_split[i], out_split[i + 1], tok_off.data()));
+        }
+    else if (hk && hk->after_out)
+        Q3A_TRY(hk->after_out(0, 0, n_utts, tok_off.data()));
     prof.end(sp_x);
     return Q3A_OK;
 }
 
 static int encode_dispatch(q3a_encoder* e, const float* mel_dev, const int64_t* mel_off, const float* max_dev,
                            const int* n_frames, int n_utts, int mode, float* out_dev, int64_t* tok_off,
-                           cudaStream_t st) {
+                           cudaStream_t st, const PartHooks* hk = nullptr) {
     if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
     if (e->fmt == OP_F16)
-        return encode_core<__half>(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st);
-    return encode_core<__nv_bfloat16>(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st);
+        return encode_core<__half>(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st, hk);
+    return encode_core<__nv_bfloat16>(e, mel_dev, mel_off, max_dev, n_frames, n_utts, mode, out_dev, tok_off, st, hk);
 }
 
 // ---- loading ------------------------------------------------------------------------------------------------
@@ -494,6 +575,8 @@ extern "C" void q3a_encoder_free(q3a_encoder* e) {
         if (e->ev_in[i]) cudaEventDestroy(e->ev_in[i]);
         if (e->ev_comp[i]) cudaEventDestroy(e->ev_comp[i]);
         if (e->ev_out[i]) cudaEventDestroy(e->ev_out[i]);
+        for (auto ev : e->ev_part_in[i]) if (ev) cudaEventDestroy(ev);
+        for (auto ev : e->ev_part_out[i]) if (ev) cudaEventDestroy(ev);
     }
     if (e->copy_in) cudaStreamDestroy(e->copy_in);
     if (e->copy_out) cudaStreamDestroy(e->copy_out);
@@ -524,6 +607,10 @@ extern "C" int q3a_encoder_load(const char* gguf_path, int device, int operand_d
             ok = cudaEventCreateWithFlags(&e->ev_in[i], cudaEventDisableTiming) == cudaSuccess &&
                  cudaEventCreateWithFlags(&e->ev_comp[i], cudaEventDisableTiming) == cudaSuccess &&
                  cudaEventCreateWithFlags(&e->ev_out[i], cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; i < 2 && ok; ++i) {
+            for (auto& ev : e->ev_part_in[i]) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+            for (auto& ev : e->ev_part_out[i]) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
+        }
         if (!ok) { set_error("cudaStreamCreate / cudaEventCreate failed"); rc = Q3A_ERR_CUDA; }
     }
     if (rc != Q3A_OK) { q3a_encoder_free(e); return rc; }
@@ -573,16 +660,16 @@ extern "C" int q3a_encoder_encode_device(q3a_encoder* e, const float* mel_dev, c
     return prof_collect(e, st);
 }
 
-// Splits [0, n) into passes.  A pass bounds the stem workspace (kMaxChunksPerPass) and is the unit of the
-// upload | compute | download pipeline of the host-pointer entry points: a call with enough work is cut into
-// at least two balanced passes so that the PCIe copies of one pass hide under the kernels of the other.
+// Splits [0, n) into passes.  A pass bounds the stem workspace (kMaxChunksPerPass); consecutive passes of the
+// host-pointer entry points overlap as upload | compute | download.  Inside a pass the copies overlap the
+// kernels at a finer grain (PartHooks), which measured better than cutting a batch that fits into two passes
+// (each pass pays its own ramp-up and tail: 64 x 30 s ran 24.8 ms as 2 passes, 24.0 ms as one pass with parts).
+// Q3A_PIPELINE_MIN_CHUNKS=<n> forces a split into two passes once a call has 2n chunks (experiments only).
 // Results do not depend on the split (the kernels are batch-invariant).
-constexpr int kPipelineMinChunks = 640;   // ~8300 tokens: below this a pass no longer fills the GEMM waves
-
-static int pipeline_min_chunks() {          // Q3A_PIPELINE_MIN_CHUNKS overrides (0 disables the split)
+static int pipeline_min_chunks() {
     static const int v = [] {
         const char* e = getenv("Q3A_PIPELINE_MIN_CHUNKS");
-        const int x = e ? atoi(e) : kPipelineMinChunks;
+        const int x = e ? atoi(e) : 0;
         return x > 0 ? x : (1 << 30);
     }();
     return v;
@@ -597,7 +684,7 @@ static void plan_passes(const int* n_frames, int n, int mode, std::vector<int>& 
     long long total = 0;
     for (int i = 0; i < n; ++i) total += chunks_of(n_frames[i], mode);
     long long n_pass = (total + kMaxChunksPerPass - 1) / kMaxChunksPerPass;
-    if (n_pass < 2 && total >= 2LL * pipeline_min_chunks()) n_pass = total / pipeline_min_chunks() >= 3 && getenv("Q3A_PIPELINE_3") ? 3 : 2;
+    if (n_pass < 2 && total >= 2LL * pipeline_min_chunks()) n_pass = 2;
     if (n_pass < 1) n_pass = 1;
     const long long target = (total + n_pass - 1) / n_pass;
     bounds.assign(1, 0);
@@ -610,26 +697,62 @@ static void plan_passes(const int* n_frames, int n, int mode, std::vector<int>& 
     bounds.push_back(n);
 }
 
+// Cuts [0, n) into at most `parts` runs of roughly equal weight.
+static std::vector<int> balanced_split(const std::vector<long long>& weight, int parts) {
+    const int n = (int)weight.size();
+    long long total = 0;
+    for (long long w : weight) total += w;
+    std::vector<int> sp{0};
+    long long acc = 0;
+    for (int i = 0; i < n; ++i) {
+        acc += weight[i];
+        const int k = (int)sp.size();                       // next boundary to place
+        if (k < parts && i + 1 < n && acc * parts >= total * k) sp.push_back(i + 1);
+    }
+    sp.push_back(n);
+    return sp;
+}
+
 // The pipeline itself.  `in[i]` has `in_elems[i]` floats on the host; `compute(u0, nu, in_dev, in_off, out_dev,
-// tok_off)` enqueues the pass on e->stream and fills tok_off[0..nu] (token rows relative to the pass).
+// hooks)` enqueues the pass on e->stream.  Inside a pass the upload is cut into kInParts and the download into
+// kOutParts (PartHooks): the stem of part i runs while part i+1 is still on the wire, and the rows of the first
+// output part travel back while the second runs its last layers.
+constexpr long long kSplitMinBytes = 16ll << 20;
+
 template <class Compute>
 static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in_elems, const int* n_frames, int n,
                            int mode, int width, float* const* out, int* n_tokens, Compute compute) {
+    static const bool trace = getenv("Q3A_TRACE") != nullptr;
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto stamp = [&](const char* what) {
+        if (trace) fprintf(stderr, "[q3a trace] %-28s %8.3f ms\n", what,
+                           std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
+    };
     std::vector<int> bounds;
     plan_passes(n_frames, n, mode, bounds);
     const int n_pass = (int)bounds.size() - 1;
     DevBuf* sin[2] = {&e->stage_in, &e->stage_in2};
     DevBuf* sout[2] = {&e->stage_out, &e->stage_out2};
-    // offsets and buffer sizes of every pass, reserved up front (nothing is in flight yet)
+    // offsets, partition and buffer sizes of every pass, reserved up front (nothing is in flight yet)
     std::vector<std::vector<int64_t>> ioff(n_pass);
-    std::vector<int> T(n_pass, 0);
+    std::vector<std::vector<int>> in_split(n_pass), out_split(n_pass);
     size_t need_in[2] = {0, 0}, need_out[2] = {0, 0};
+    const bool split_ok = getenv("Q3A_NO_PART_OVERLAP") == nullptr;
     for (int p = 0; p < n_pass; ++p) {
         const int u0 = bounds[p], nu = bounds[p + 1] - u0;
         q3a_pack_offsets(in_elems + u0, nu, 1, 64, ioff[p]);
-        for (int i = 0; i < nu; ++i) T[p] += encoder_n_tokens(n_frames[u0 + i], mode);
+        std::vector<long long> w_in(nu), w_out(nu);
+        long long T = 0;
+        for (int i = 0; i < nu; ++i) {
+            w_in[i] = in_elems[u0 + i];
+            w_out[i] = encoder_n_tokens(n_frames[u0 + i], mode);
+            T += w_out[i];
+        }
+        const long long in_bytes = 4ll * ioff[p][nu], out_bytes = 4ll * T * width;
+        in_split[p] = balanced_split(w_in, split_ok && in_bytes >= kSplitMinBytes ? q3a_encoder::kInParts : 1);
+        out_split[p] = balanced_split(w_out, split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY ? q3a_encoder::kOutParts : 1);
         need_in[p & 1] = std::max(need_in[p & 1], sizeof(float) * (size_t)(ioff[p][nu] + 64));
-        need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)T[p] * width + 64));
+        need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)T * width + 64));
     }
     for (int b = 0; b < 2; ++b) {
         if (need_in[b]) Q3A_TRY(sin[b]->reserve(need_in[b]));
@@ -640,39 +763,59 @@ static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in
         return rc;
     };
 #define PIPE_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error(std::string(#x) + ": " + cudaGetErrorString(e_)); return drain(Q3A_ERR_CUDA); } } while (0)
+#define HOOK_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error(std::string(#x) + ": " + cudaGetErrorString(e_)); return (int)Q3A_ERR_CUDA; } } while (0)
     auto upload = [&](int p) -> int {
-        const int b = p & 1, u0 = bounds[p], nu = bounds[p + 1] - u0;
+        const int b = p & 1, u0 = bounds[p];
         if (p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->copy_in, e->ev_comp[b], 0));   // pass p-2 has consumed the buffer
-        for (int i = 0; i < nu; ++i)
-            if (in_elems[u0 + i] > 0)
-                PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<float>() + ioff[p][i], in[u0 + i], sizeof(float) * in_elems[u0 + i],
-                                          cudaMemcpyHostToDevice, e->copy_in));
-        PIPE_CUDA(cudaEventRecord(e->ev_in[b], e->copy_in));
+        const std::vector<int>& sp = in_split[p];
+        for (size_t part = 0; part + 1 < sp.size(); ++part) {
+            for (int i = sp[part]; i < sp[part + 1]; ++i)
+                if (in_elems[u0 + i] > 0)
+                    PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<float>() + ioff[p][i], in[u0 + i], sizeof(float) * in_elems[u0 + i],
+                                              cudaMemcpyHostToDevice, e->copy_in));
+            PIPE_CUDA(cudaEventRecord(e->ev_part_in[b][part], e->copy_in));
+        }
         return Q3A_OK;
     };
+    stamp("planned");
     if (n_pass > 0) { const int rc = upload(0); if (rc != Q3A_OK) return rc; }
+    stamp("upload 0 enqueued");
     for (int p = 0; p < n_pass; ++p) {
         const int b = p & 1, u0 = bounds[p], nu = bounds[p + 1] - u0;
         if (p + 1 < n_pass) { const int rc = upload(p + 1); if (rc != Q3A_OK) return rc; }
-        PIPE_CUDA(cudaStreamWaitEvent(e->stream, e->ev_in[b], 0));
         if (p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->stream, e->ev_out[b], 0));       // pass p-2 has been downloaded
-        std::vector<int64_t> toff(nu + 1, 0);
-        const int rc = compute(u0, nu, sin[b]->as<float>(), ioff[p].data(), sout[b]->as<float>(), toff.data());
+        PartHooks hk;
+        hk.in_split = in_split[p];
+        hk.out_split = out_split[p];
+        hk.before_stem = [&, b](int part, int, int) -> int {
+            if (part == 0) stamp("first before_stem");
+            HOOK_CUDA(cudaStreamWaitEvent(e->stream, e->ev_part_in[b][part], 0));
+            return Q3A_OK;
+        };
+        hk.after_out = [&, b, u0](int part, int ua, int ub, const int64_t* toff) -> int {
+            HOOK_CUDA(cudaEventRecord(e->ev_part_out[b][part], e->stream));
+            HOOK_CUDA(cudaStreamWaitEvent(e->copy_out, e->ev_part_out[b][part], 0));
+            for (int i = ua; i < ub; ++i) {
+                const int64_t rows = toff[i + 1] - toff[i];
+                if (n_tokens) n_tokens[u0 + i] = (int)rows;
+                if (rows > 0)
+                    HOOK_CUDA(cudaMemcpyAsync(out[u0 + i], sout[b]->as<float>() + toff[i] * width, sizeof(float) * rows * width,
+                                              cudaMemcpyDeviceToHost, e->copy_out));
+            }
+            return Q3A_OK;
+        };
+        const int rc = compute(u0, nu, sin[b]->as<float>(), ioff[p].data(), sout[b]->as<float>(), &hk);
         if (rc != Q3A_OK) return drain(rc);
+        stamp("compute enqueued");
         PIPE_CUDA(cudaEventRecord(e->ev_comp[b], e->stream));
-        PIPE_CUDA(cudaStreamWaitEvent(e->copy_out, e->ev_comp[b], 0));
-        for (int i = 0; i < nu; ++i) {
-            const int64_t rows = toff[i + 1] - toff[i];
-            if (n_tokens) n_tokens[u0 + i] = (int)rows;
-            if (rows > 0)
-                PIPE_CUDA(cudaMemcpyAsync(out[u0 + i], sout[b]->as<float>() + toff[i] * width, sizeof(float) * rows * width,
-                                          cudaMemcpyDeviceToHost, e->copy_out));
-        }
         PIPE_CUDA(cudaEventRecord(e->ev_out[b], e->copy_out));
     }
+    if (trace) { cudaStreamSynchronize(e->copy_in); stamp("uploads done"); cudaStreamSynchronize(e->stream); stamp("compute done"); }
     PIPE_CUDA(cudaStreamSynchronize(e->copy_out));
     PIPE_CUDA(cudaStreamSynchronize(e->stream));
+    stamp("all done");
 #undef PIPE_CUDA
+#undef HOOK_CUDA
     return Q3A_OK;
 }
 
@@ -694,15 +837,15 @@ extern "C" int q3a_encoder_encode_batch(q3a_encoder* e, const float* const* mel,
     std::vector<int> elems(n_utts);
     for (int i = 0; i < n_utts; ++i) elems[i] = n_mel * n_frames[i];
     Q3A_TRY(run_host_passes(e, mel, elems.data(), n_frames, n_utts, mode, width, out, n_tokens,
-                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, int64_t* toff) {
-                                return encode_dispatch(e, in_dev, in_off, nullptr, n_frames + u0, nu, mode, out_dev, toff, e->stream);
+                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
+                                return encode_dispatch(e, in_dev, in_off, nullptr, n_frames + u0, nu, mode, out_dev, nullptr, e->stream, hk);
                             }));
     return prof_collect(e, e->stream);
 }
 
 // mel (raw log10 + per-clip max) and encoder (clamp fused into conv1's loads) for clips on the device
 static int pcm_core(q3a_frontend* fe, q3a_encoder* e, const float* pcm_dev, const int64_t* pcm_off, const int* n_samples,
-                    int n_clips, int mode, float* out_dev, int64_t* tok_off, cudaStream_t st) {
+                    int n_clips, int mode, float* out_dev, int64_t* tok_off, cudaStream_t st, const PartHooks* hk = nullptr) {
     if (fe->n_mel != e->hp.n_mel_bins) {
         set_error("Mel bins mismatch: expected " + std::to_string(e->hp.n_mel_bins) + ", got " + std::to_string(fe->n_mel));
         return Q3A_ERR_ARG;
@@ -718,12 +861,20 @@ static int pcm_core(q3a_frontend* fe, q3a_encoder* e, const float* pcm_dev, cons
     Q3A_TRY(e->stage_mel.reserve(sizeof(float) * (size_t)(moff[n_clips] + 64)));
     Q3A_TRY(e->stage_max.reserve(sizeof(float) * (size_t)(n_clips + 1)));
     Prof prof{e, st};
-    const int sp = prof.begin(SP_MEL);
-    Q3A_TRY(mel_launch(fe, pcm_dev, pcm_off, n_samples, n_clips, e->stage_mel.as<float>(), moff.data(),
-                       e->stage_max.as<float>(), 0, st));
-    prof.end(sp);
+    // the mel kernels of a part run right before its stem (after the part's upload has landed)
+    PartHooks mine;
+    if (hk) { mine.in_split = hk->in_split; mine.out_split = hk->out_split; mine.after_out = hk->after_out; mine.tail_layers = hk->tail_layers; }
+    mine.before_stem = [&](int part, int ua, int ub) -> int {
+        if (hk && hk->before_stem) Q3A_TRY(hk->before_stem(part, ua, ub));
+        if (ub <= ua) return Q3A_OK;
+        const int sp = prof.begin(SP_MEL);
+        Q3A_TRY(mel_launch(fe, pcm_dev, pcm_off + ua, n_samples + ua, ub - ua, e->stage_mel.as<float>(), moff.data() + ua,
+                           e->stage_max.as<float>() + ua, 0, st));
+        prof.end(sp);
+        return Q3A_OK;
+    };
     return encode_dispatch(e, e->stage_mel.as<float>(), moff.data(), e->stage_max.as<float>(), nf.data(), n_clips, mode,
-                           out_dev, tok_off, st);
+                           out_dev, tok_off, st, &mine);
 }
 
 extern "C" int q3a_encode_pcm_device(q3a_frontend* fe, q3a_encoder* e, const float* pcm_dev, const int64_t* pcm_off,
@@ -756,8 +907,8 @@ extern "C" int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* e, const floa
     std::vector<int> nf(n_clips);
     for (int i = 0; i < n_clips; ++i) nf[i] = n_samples[i] / 160;
     Q3A_TRY(run_host_passes(e, pcm, n_samples, nf.data(), n_clips, mode, width, out, n_tokens,
-                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, int64_t* toff) {
-                                return pcm_core(fe, e, in_dev, in_off, n_samples + u0, nu, mode, out_dev, toff, e->stream);
+                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
+                                return pcm_core(fe, e, in_dev, in_off, n_samples + u0, nu, mode, out_dev, nullptr, e->stream, hk);
                             }));
     return prof_collect(e, e->stream);
 }

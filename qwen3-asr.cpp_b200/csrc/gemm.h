@@ -30,7 +30,9 @@ int gemm_linear(EpiKind kind, int fmt, const LinearArgs& a, cudaStream_t stream)
 
 struct ConvArgs {
     const void* planes = nullptr;  // input [4][R_cap][Fh][C] 16-bit
-    int R_cap = 0, R_used = 0, Fh = 0, C = 0;
+    int R_cap = 0, R_used = 0, Fh = 0, C = 0;   // R_cap: rows between planes (stride); R_used: rows this launch covers
+    int R_map = 0;                 // rows the tensor map may address from `planes` (0: R_cap); smaller when `planes`
+                                   // points into the middle of the arena (a sub-range of chunks)
     const void* w = nullptr;       // [N][9 * cpad] 16-bit, cpad = ceil(C/64)*64, k = tap*cpad + c
     int N = 0;
     const float* bias = nullptr;

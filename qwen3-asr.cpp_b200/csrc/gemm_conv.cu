@@ -16,7 +16,7 @@ static int launch_conv(const ConvArgs& a, const Epi& epi, cudaStream_t stream) {
     const int cpad = c_blocks * kBlockK;
     CUtensorMap ta, tb;
     {
-        uint64_t dims[4] = {(uint64_t)a.C, (uint64_t)a.Fh, (uint64_t)a.R_cap, 4};
+        uint64_t dims[4] = {(uint64_t)a.C, (uint64_t)a.Fh, (uint64_t)(a.R_map > 0 ? a.R_map : a.R_cap), 4};
         uint64_t strides[3] = {(uint64_t)a.C * 2, (uint64_t)a.Fh * a.C * 2, (uint64_t)a.R_cap * a.Fh * a.C * 2};
         uint32_t box[4] = {64, (uint32_t)a.Fh, (uint32_t)(kBlockM / a.Fh), 1};
         Q3A_TRY(make_tmap_16bit(&ta, a.planes, 4, dims, strides, box));

@@ -34,7 +34,7 @@ bool conv1_tc_supported(int C);
 void conv1_tc_weight_image(const float* w /*[C][9]: df*3+dt*/, int C, std::vector<uint8_t>& image);
 template <class OpT>
 int conv1_tc_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks, int P2, const float* clip_max,
-                    const void* w_image, const float* bias, int C, OpT* planes, int R_cap, cudaStream_t stream);
+                    const void* w_image, const float* bias, int C, OpT* planes, int R_cap, int row0, cudaStream_t stream);
 
 // LayerNorm over rows of x [T][d] f32 -> 16-bit operand rows (audio_encoder.cpp:441-448)
 template <class OpT>

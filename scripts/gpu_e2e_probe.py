@@ -39,3 +39,31 @@ if os.environ.get("PROBE_COPY"):
     torch.cuda.synchronize(); t0 = time.perf_counter()
     enc.encode_pcm_device(fe, d.data_ptr(), pcm_off, [n] * BATCH, o.data_ptr(), B.MODE_ASR, st)
     torch.cuda.synchronize(); print(f"device-only single call {(time.perf_counter()-t0)*1e3:.2f} ms")
+if os.environ.get("PROBE_OVERLAP"):
+    d = torch.empty((BATCH, n), dtype=torch.float32, device="cuda"); d.copy_(host)
+    o = torch.empty((T * BATCH, 1024), dtype=torch.float32, device="cuda"); oh = torch.empty((T * BATCH, 1024), dtype=torch.float32).pin_memory()
+    d2 = torch.empty_like(d)
+    pcm_off = [i * n for i in range(BATCH)]
+    s1, s2, s3 = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+    def ev(): return torch.cuda.Event(enable_timing=True)
+    for load in (False, True):
+        torch.cuda.synchronize()
+        a0, a1, b0, b1, c0, c1 = ev(), ev(), ev(), ev(), ev(), ev()
+        if load:
+            with torch.cuda.stream(s1):
+                a0.record(s1)
+                for _ in range(2): enc.encode_pcm_device(fe, d.data_ptr(), pcm_off, [n] * BATCH, o.data_ptr(), B.MODE_ASR, s1.cuda_stream)
+                a1.record(s1)
+        with torch.cuda.stream(s2):
+            b0.record(s2); d2.copy_(host, non_blocking=True); b1.record(s2)
+        with torch.cuda.stream(s3):
+            c0.record(s3); oh.copy_(o, non_blocking=True); c1.record(s3)
+        torch.cuda.synchronize()
+        print(f"under load={load}: h2d {b0.elapsed_time(b1):.2f} ms, d2h {c0.elapsed_time(c1):.2f} ms" + (f", compute x2 {a0.elapsed_time(a1):.2f} ms" if load else ""))
+if os.environ.get("PROBE_SPANS"):
+    enc.set_profiling(True)
+    for _ in range(3):
+        t0 = time.perf_counter(); call(); dt = (time.perf_counter() - t0) * 1e3
+        tm = enc.timings()
+        print(f"profiled e2e call {dt:.2f} ms: mel {tm.mel_ms:.2f} stem-span {tm.conv_chunk_ms:.2f} xfmr-span {tm.transformer_ms:.2f} gemm {tm.gemm_ms:.2f} attn {tm.attention_ms:.2f} other {tm.other_ms:.2f}")
+    enc.set_profiling(False)
