@@ -23,34 +23,47 @@
 #include "tc.cuh"
 #include "tmap.h"
 
+#include <cstdlib>
+
 namespace q3a {
 
 constexpr int kHd = 64;
 constexpr int kQT = 128;                 // queries per CTA
-constexpr int kKT = 128;                 // keys per block
 constexpr int kTileBytes = 128 * 64 * 2; // 16 KB: [128 rows][64 x 16-bit]
-constexpr int kAttnSmem = kTileBytes /*Q*/ + 4 * kTileBytes /*K,V x2*/ + 2 * kTileBytes /*P*/ + 128;
-constexpr int kAttnTmemCols = 256;       // S: columns [0,128), O: columns [128,192)
+// KT = keys per block (128 or 64).  128: fewer blocks, 2 CTAs/SM (255 registers, 112 KB smem, 256 TMEM columns).
+// 64: half the per-thread state, so 3 CTAs/SM fit (168 registers, 64 KB, 128 columns) and hide each other's
+// barrier / TMEM-load latency better.
+template <int KT> struct AttnCfg {
+    static constexpr int kKV = KT * 64 * 2;                    // one K or V block
+    static constexpr int kP = 128 * KT * 2;                    // P: KT/64 sub-tiles of [128][64]
+    static constexpr int kSmem = kTileBytes + 4 * kKV + kP + 128;
+    static constexpr int kTmemCols = KT == 128 ? 256 : 128;    // S: columns [0,KT), O: columns [KT,KT+64)
+    static constexpr int kCtas = KT == 128 ? 2 : 3;
+};
 constexpr float kRescaleThreshold = 8.0f;   // log2 units: p <= 2^8 between rescales
 
-template <class OpT>
-__global__ void __launch_bounds__(128, 2)
-attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* __restrict__ tiles,
-                 OpT* __restrict__ out, int d_model) {
+template <class OpT, int kKT>
+__global__ void __launch_bounds__(128, AttnCfg<kKT>::kCtas)
+attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_constant__ CUtensorMap tmap_kv,
+                 const AttnTile* __restrict__ tiles, OpT* __restrict__ out, int d_model) {
+    using Cfg = AttnCfg<kKT>;
+    constexpr int kKV = Cfg::kKV;
+    constexpr int kAttnTmemCols = Cfg::kTmemCols;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     const uint32_t base = tc::smem_u32(smem_raw);
     if (base & 1023u) { asm volatile("trap;"); }          // the swizzled tiles need 1024-byte alignment
     const uint32_t sQ = base;
-    auto sK = [&](int b) { return base + kTileBytes * (1 + b); };
-    auto sV = [&](int b) { return base + kTileBytes * (3 + b); };
-    const uint32_t sP = base + 5 * kTileBytes;
-    uint8_t* gP = smem_raw + 5 * kTileBytes;
-    const uint32_t bars = base + 7 * kTileBytes;
+    auto sK = [&](int b) { return base + kTileBytes + kKV * b; };
+    auto sV = [&](int b) { return base + kTileBytes + kKV * (2 + b); };
+    constexpr int kPOff = kTileBytes + 4 * kKV, kBarOff = kPOff + Cfg::kP;
+    const uint32_t sP = base + kPOff;
+    uint8_t* gP = smem_raw + kPOff;
+    const uint32_t bars = base + kBarOff;
     const uint32_t bar_q = bars, bar_s = bars + 8, bar_o = bars + 16;
     auto bar_k = [&](int b) { return bars + 24 + 8 * b; };
     auto bar_v = [&](int b) { return bars + 40 + 8 * b; };
     const uint32_t tmem_slot = bars + 56;
-    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + 7 * kTileBytes + 56);
+    volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + kBarOff + 56);
 
     const int tid = threadIdx.x, warp = tid >> 5;
     const AttnTile t = tiles[blockIdx.x];
@@ -86,6 +99,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
         if (tc::elect_one()) {
             pdl_trigger();
             tc::prefetch_tmap(&tmap_qkv);
+            tc::prefetch_tmap(&tmap_kv);
             tc::mbar_init(bar_q, 1); tc::mbar_init(bar_s, 1); tc::mbar_init(bar_o, 1);
             tc::mbar_init(bar_k(0), 1); tc::mbar_init(bar_k(1), 1);
             tc::mbar_init(bar_v(0), 1); tc::mbar_init(bar_v(1), 1);
@@ -93,13 +107,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             pdl_wait();                                    // qkv is the previous kernel's output
             tc::mbar_arrive_expect_tx(bar_q, kTileBytes);
             tc::tma_load_2d(sQ, &tmap_qkv, bar_q, col_q, t.q0);
-            tc::mbar_arrive_expect_tx(bar_k(0), kTileBytes);
-            tc::tma_load_2d(sK(0), &tmap_qkv, bar_k(0), col_k, t.seg_start);
-            tc::mbar_arrive_expect_tx(bar_v(0), kTileBytes);
-            tc::tma_load_2d(sV(0), &tmap_qkv, bar_v(0), col_v, t.seg_start);
+            tc::mbar_arrive_expect_tx(bar_k(0), kKV);
+            tc::tma_load_2d(sK(0), &tmap_kv, bar_k(0), col_k, t.seg_start);
+            tc::mbar_arrive_expect_tx(bar_v(0), kKV);
+            tc::tma_load_2d(sV(0), &tmap_kv, bar_v(0), col_v, t.seg_start);
             if (nkv > 1) {
-                tc::mbar_arrive_expect_tx(bar_k(1), kTileBytes);
-                tc::tma_load_2d(sK(1), &tmap_qkv, bar_k(1), col_k, t.seg_start + kKT);
+                tc::mbar_arrive_expect_tx(bar_k(1), kKV);
+                tc::tma_load_2d(sK(1), &tmap_kv, bar_k(1), col_k, t.seg_start + kKT);
             }
         }
         __syncwarp();
@@ -127,10 +141,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
         // ---- S_j -> registers ---------------------------------------------------------------------
         tc::mbar_wait(bar_s, j & 1);
         tc::fence_after_sync();
-        uint32_t s[128];
+        uint32_t s[kKT];
         if (row_live) {
 #pragma unroll
-            for (int c = 0; c < 4; ++c)
+            for (int c = 0; c < kKT / 32; ++c)
                 if (c * 32 < nk) tc::tmem_ld_32x32b_x32(t_row + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
             tc::tmem_ld_wait();
         }
@@ -140,8 +154,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             tc::fence_after_sync();
             if (j + 2 < nkv) {
                 if (tc::elect_one()) {
-                    tc::mbar_arrive_expect_tx(bar_k(j & 1), kTileBytes);
-                    tc::tma_load_2d(sK(j & 1), &tmap_qkv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
+                    tc::mbar_arrive_expect_tx(bar_k(j & 1), kKV);
+                    tc::tma_load_2d(sK(j & 1), &tmap_kv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
                 }
                 __syncwarp();
             }
@@ -154,7 +168,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;   // independent chains
             if (n_valid == kKT) {
 #pragma unroll
-                for (int i = 0; i < 128; i += 8) {
+                for (int i = 0; i < kKT; i += 8) {
                     mx0 = fmaxf(mx0, fmaxf(__uint_as_float(s[i + 0]), __uint_as_float(s[i + 1])));
                     mx1 = fmaxf(mx1, fmaxf(__uint_as_float(s[i + 2]), __uint_as_float(s[i + 3])));
                     mx2 = fmaxf(mx2, fmaxf(__uint_as_float(s[i + 4]), __uint_as_float(s[i + 5])));
@@ -162,7 +176,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
                 }
             } else {
 #pragma unroll
-                for (int i = 0; i < 128; i += 16) {
+                for (int i = 0; i < kKT; i += 16) {
                     if (i < nk) {                          // warp-uniform: 16-key groups past the end are skipped
 #pragma unroll
                         for (int e = 0; e < 16; e += 4) {
@@ -189,11 +203,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
 #pragma unroll
                     for (int c = 0; c < kHd; c += 32) {
                         uint32_t r[32];
-                        tc::tmem_ld_32x32b_x32(t_row + 128 + c, r);
+                        tc::tmem_ld_32x32b_x32(t_row + kKT + c, r);
                         tc::tmem_ld_wait();
 #pragma unroll
                         for (int i = 0; i < 32; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * alpha);
-                        tc::tmem_st_32x32b_x32(t_row + 128 + c, r);
+                        tc::tmem_st_32x32b_x32(t_row + kKT + c, r);
                     }
                     tc::tmem_st_wait();
                 }
@@ -202,7 +216,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             if (n_valid == kKT) {
                 float ps1 = 0.0f;
 #pragma unroll
-                for (int i = 0; i < 128; i += 2) {
+                for (int i = 0; i < kKT; i += 2) {
                     const float p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i]), kScale, neg_m));
                     const float p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + 1]), kScale, neg_m));
                     psum += p0; ps1 += p1;
@@ -211,7 +225,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
                 psum += ps1;
             } else {
 #pragma unroll
-                for (int i = 0; i < 128; i += 16) {
+                for (int i = 0; i < kKT; i += 16) {
                     if (i < nk) {                          // warp-uniform; P columns >= nk are never read
 #pragma unroll
                         for (int e = 0; e < 16; e += 2) {
@@ -231,7 +245,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
         if (row_live) {
             // 64-key sub-tile c, 16-byte chunks XOR-swizzled with row % 8
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
+            for (int c = 0; c < kKT / 64; ++c) {
                 if (c * 64 < nk) {
                     uint8_t* prow = gP + c * kTileBytes + tid * 128;
 #pragma unroll
@@ -252,8 +266,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             if (j + 1 < nkv) {                              // V_{j-1}'s buffer is free: fetch V_{j+1}
                 const int nb = (j + 1) & 1;
                 if (tc::elect_one()) {
-                    tc::mbar_arrive_expect_tx(bar_v(nb), kTileBytes);
-                    tc::tma_load_2d(sV(nb), &tmap_qkv, bar_v(nb), col_v, t.seg_start + (j + 1) * kKT);
+                    tc::mbar_arrive_expect_tx(bar_v(nb), kKV);
+                    tc::tma_load_2d(sV(nb), &tmap_kv, bar_v(nb), col_v, t.seg_start + (j + 1) * kKT);
                 }
                 __syncwarp();
             }
@@ -265,8 +279,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
             const int ks = nk / 16;
             if (tc::elect_one()) {
 #pragma unroll
-                for (int k = 0; k < 8; ++k)                 // 16 key rows of V = 2048 B
-                    if (k < ks) tc::mma_f16_ss(tmem + 128, (k < 4 ? a0 : a1) + 2 * (k & 3), b0 + (uint64_t)k * 128, idesc,
+                for (int k = 0; k < kKT / 16; ++k)          // 16 key rows of V = 2048 B
+                    if (k < ks) tc::mma_f16_ss(tmem + kKT, (k < 4 ? a0 : a1) + 2 * (k & 3), b0 + (uint64_t)k * 128, idesc,
                                                (j | k) != 0);
                 tc::mma_commit(bar_o);
             }
@@ -284,7 +298,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* _
 #pragma unroll
         for (int c = 0; c < kHd; c += 32) {
             uint32_t r[32];
-            tc::tmem_ld_32x32b_x32(t_row + 128 + c, r);
+            tc::tmem_ld_32x32b_x32(t_row + kKT + c, r);
             tc::tmem_ld_wait();
             if (row < t.seg_end) {
 #pragma unroll
@@ -320,26 +334,36 @@ double attention_flops(const int* cu_seqlens, int n_seg, int n_heads) {
     return f;
 }
 
+template <class OpT, int KT>
+static int attention_launch_kt(const void* qkv, void* out, int T, int d, const AttnTile* tiles_dev, int n_tiles, int n_heads,
+                               cudaStream_t stream) {
+    using Cfg = AttnCfg<KT>;
+    CUtensorMap tm_q, tm_kv;
+    Q3A_TRY(make_tmap_2d(&tm_q, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, 128));
+    Q3A_TRY(make_tmap_2d(&tm_kv, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, KT));
+    auto kern = attention_kernel<OpT, KT>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        Q3A_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem));
+        attr_set = true;
+    }
+    Q3A_CUDA(launch_pdl(kern, dim3(n_tiles, n_heads), dim3(128), Cfg::kSmem, stream, tm_q, tm_kv, tiles_dev, (OpT*)out, d));
+    ++g_launch_counter;
+    Q3A_CUDA(cudaGetLastError());
+    return Q3A_OK;
+}
+
 int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnTile* tiles_dev, int n_tiles, int fmt,
                      cudaStream_t stream) {
     if (n_tiles == 0 || T == 0) return Q3A_OK;
     const int d = n_heads * kHd;
-    CUtensorMap tm;
-    Q3A_TRY(make_tmap_2d(&tm, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, 128));
-    static bool attr_set = false;
-    if (!attr_set) {
-        Q3A_CUDA(cudaFuncSetAttribute(attention_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-        Q3A_CUDA(cudaFuncSetAttribute(attention_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, kAttnSmem));
-        attr_set = true;
+    static const int kt = [] { const char* e = getenv("Q3A_ATTN_KT"); return e && atoi(e) == 128 ? 128 : 64; }();
+    if (kt == 128) {
+        if (fmt == OP_F16) return attention_launch_kt<__half, 128>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
+        return attention_launch_kt<__nv_bfloat16, 128>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
     }
-    dim3 grid(n_tiles, n_heads);
-    if (fmt == OP_F16)
-        Q3A_CUDA(launch_pdl(attention_kernel<__half>, grid, dim3(128), kAttnSmem, stream, tm, tiles_dev, (__half*)out, d));
-    else
-        Q3A_CUDA(launch_pdl(attention_kernel<__nv_bfloat16>, grid, dim3(128), kAttnSmem, stream, tm, tiles_dev, (__nv_bfloat16*)out, d));
-    ++g_launch_counter;
-    Q3A_CUDA(cudaGetLastError());
-    return Q3A_OK;
+    if (fmt == OP_F16) return attention_launch_kt<__half, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
+    return attention_launch_kt<__nv_bfloat16, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
 }
 
 }  // namespace q3a

@@ -157,6 +157,31 @@ def test_pcm_path_batch_invariance_and_full_size(lib, asr_model, filters):
     enc.close(); fe.close()
 
 
+def test_copy_overlap_partitions_do_not_change_results(lib, asr_model, monkeypatch):
+    """The host-pointer call overlaps PCIe copies with kernels by running the stem per upload part and the last
+    layers per download part (and, when forced, by cutting the call into two passes).  Ragged 2-40 s clips, all
+    three schedules: every clip's features are bit-identical."""
+    shape, paths, Ws = asr_model
+    enc = B.Encoder(paths["f16"], 0, B.OP_BF16)
+    fe = B.Frontend(0)
+    rng = np.random.default_rng(7)
+    clips = [synth.synth_audio(700 + i, int(rng.integers(2 * 16000, 40 * 16000))) for i in range(48)]
+    clips[17] = clips[17][:0]                                 # an empty clip in the middle of a part
+    parts = enc.encode_pcm_batch(fe, clips, B.MODE_ASR)
+    monkeypatch.setenv("Q3A_NO_PART_OVERLAP", "1")
+    plain = enc.encode_pcm_batch(fe, clips, B.MODE_ASR)
+    monkeypatch.delenv("Q3A_NO_PART_OVERLAP")
+    for a, b, c in zip(parts, plain, clips):
+        assert a.shape == (synth.chunk_tokens(len(c) // 160), 1024)
+        assert np.array_equal(a, b)
+    mels = fe.mel_batch(clips)
+    via_mel = enc.encode_batch(mels, B.MODE_ASR)               # host mel in, same partitioning machinery
+    for a, b in zip(parts, via_mel):
+        cos, rel = compare(a, b) if a.size else (1.0, 0.0)
+        assert cos >= 0.99999 and rel <= 2e-3                   # mel finalised on the host path vs clamp fused in conv1
+    enc.close(); fe.close()
+
+
 def test_aligner_shape_variable_length_batch(lib, filters, tmp_path):
     """BASELINE config 4 (reduced: 4 layers of the aligner width, 5-40 s utterances): padded-tail stem, 104-token windows"""
     shape = synth.EncoderShape("aligner-4l", 4, 1024, 16, 4096)

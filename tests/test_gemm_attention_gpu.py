@@ -39,7 +39,8 @@ def _attn_ref(qkv, H, cu):
     return out
 
 
-@pytest.mark.parametrize("opd,tol", [(B.OP_BF16, 2.5e-2), (B.OP_F16, 4e-3)])
+# outputs reach |o| ~ 5: half an ulp of bf16 there is 1.6e-2 from the output rounding alone, P's rounding adds ~1e-2
+@pytest.mark.parametrize("opd,tol", [(B.OP_BF16, 3e-2), (B.OP_F16, 4e-3)])
 @pytest.mark.parametrize("H,cu", [
     (2, [0, 128]), (2, [0, 16]), (1, [0, 1]), (3, [0, 100]), (14, [0, 390]), (16, [0, 104, 208, 250]),
     (2, [0, 1, 130, 400, 1596]), (4, [0, 129, 129, 257]), (14, [0, 1560]), (16, [104 * i for i in range(16)])])
