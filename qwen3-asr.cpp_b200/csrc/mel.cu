@@ -16,6 +16,7 @@
 // Algorithmic HBM bytes per clip: 4*n_samples (PCM read once) + 4*n_mel*n_len (mel written once).
 #include "mel.h"
 #include "mel_fft.cuh"
+#include "tc.cuh"
 
 #include <cmath>
 #include <cstdint>
@@ -37,11 +38,13 @@ constexpr int kS1Frames = 11;                            // frames stage 1 cover
 constexpr int kMaxTabWeights = 512, kMaxTabRows = 128;   // filterbank tables staged in smem up to this size
 
 struct MelSmem {
-    float u[kUnionFloats];            // samples (load, stage 1) then power[bin][frame] (stage 2, 3)
+    float u[2][kUnionFloats];         // per buffer: samples (load, stage 1) then power[bin][frame] (stage 2, 3);
+                                      // the other buffer receives the next tile's samples meanwhile
     float2 z[kFT][9][25];             // stage-1 output
     float w[kMaxTabWeights];          // compressed filterbank rows
     int bin0[kMaxTabRows], ptr[kMaxTabRows + 1];
     float red[16];
+    unsigned long long bar[2];        // mbarriers of the two sample buffers
 };
 
 __device__ __forceinline__ unsigned ordered_from_float(float f) {
@@ -61,8 +64,33 @@ __device__ __forceinline__ float padded_sample(const float* __restrict__ pcm, in
     return __ldg(pcm + src);
 }
 
+struct MelTile {            // where tile `tile` lives (warp-uniform arithmetic, every thread computes it)
+    int clip, f0, n_valid, n, n_len;
+    long long pcm_off, mel_off;
+    bool interior;          // its 5360 samples are one contiguous, 16-byte aligned run of the clip
+};
+
+__device__ __forceinline__ MelTile mel_tile_of(const MelClipDesc* __restrict__ clips, int n_clips, int tile) {
+    int lo = 0, hi = n_clips - 1;                        // tile0 is ascending; n_clips is small
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (__ldg(&clips[mid].tile0) <= tile) lo = mid; else hi = mid - 1;
+    }
+    const MelClipDesc cd = clips[lo];
+    MelTile t;
+    t.clip = lo; t.f0 = (tile - cd.tile0) * kFT; t.n = cd.n_samples; t.n_len = cd.n_len;
+    t.n_valid = min(kFT, cd.n_len - t.f0);
+    t.pcm_off = cd.pcm_off; t.mel_off = cd.mel_off;
+    const int p0 = t.f0 * kHop;
+    t.interior = p0 >= kPad && p0 + kTileSamples <= kPad + t.n;
+    return t;
+}
+
+// Persistent: a CTA walks tiles blockIdx.x, +gridDim.x, ...  While it computes tile i out of one sample buffer, a
+// bulk async copy (cp.async.bulk + mbarrier) already fills the other buffer with tile i+1, so the DRAM latency of
+// the PCM read is off the critical path; clip-edge tiles (reflect / zero padding) are loaded by the threads.
 __global__ void __launch_bounds__(kMelThreads, 2)
-mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restrict__ clips, int n_clips,
+mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restrict__ clips, int n_clips, int n_tiles,
                   const float* __restrict__ g_hann, const float2* __restrict__ g_tw,
                   const int* __restrict__ row_bin0, const int* __restrict__ row_ptr,
                   const float* __restrict__ weights, int n_mel, float* __restrict__ mel_base,
@@ -71,21 +99,10 @@ mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restr
     MelSmem& s = *reinterpret_cast<MelSmem*>(smem_raw);
     const int tid = threadIdx.x;
     pdl_trigger();
-    pdl_wait();
 
-    // which clip does this tile belong to?  (tile0 is ascending; n_clips is small)
-    int lo = 0, hi = n_clips - 1;
-    const int tile = blockIdx.x;
-    while (lo < hi) {
-        int mid = (lo + hi + 1) >> 1;
-        if (__ldg(&clips[mid].tile0) <= tile) lo = mid; else hi = mid - 1;
-    }
-    const MelClipDesc cd = clips[lo];
-    const int f0 = (tile - cd.tile0) * kFT;
-    const int n = cd.n_samples;
-    const int n_valid = min(kFT, cd.n_len - f0);         // frames of this tile that exist
-    const float* __restrict__ pcm = pcm_base + cd.pcm_off;
-
+    // ---- once per CTA: barriers, filterbank tables, this thread's window and twiddles ------------------
+    const uint32_t bar0 = tc::smem_u32(&s.bar[0]), bar1 = tc::smem_u32(&s.bar[1]);
+    if (tid == 0) { tc::mbar_init(bar0, 1); tc::mbar_init(bar1, 1); tc::fence_barrier_init(); }
     // filterbank tables: smem when they fit (the standard 128 x 201 bank has 396 non-zeros), else global
     const bool tab_smem = n_mel <= kMaxTabRows && __ldg(row_ptr + n_mel) <= kMaxTabWeights;
     if (tab_smem) {
@@ -97,38 +114,62 @@ mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restr
     const float* wtab = tab_smem ? s.w : weights;
     const int* b0tab = tab_smem ? s.bin0 : row_bin0;
     const int* ptab = tab_smem ? s.ptr : row_ptr;
-
-    // ---- load the tile's samples -------------------------------------------------------------
-    const int p0 = f0 * kHop;                             // first padded position of the tile
-    const int need = (n_valid - 1) * kHop + kNFft;        // samples the valid frames touch
-    if (p0 >= kPad && p0 + kTileSamples <= kPad + n) {    // interior: contiguous, 16-byte aligned
-        const float4* __restrict__ src = reinterpret_cast<const float4*>(pcm + (p0 - kPad));
-        float4* dst = reinterpret_cast<float4*>(s.u);
-        for (int i = tid; i < kTileSamples / 4; i += kMelThreads) dst[i] = __ldg(src + i);
-    } else {
-        for (int i = tid; i < kTileSamples; i += kMelThreads)
-            s.u[i] = (i < need) ? padded_sample(pcm, n, p0 + i) : 0.0f;
+    const bool s1 = tid < kS1Frames * 25;
+    const int fi = tid / 25, n1 = tid - fi * 25;
+    float hw[16];
+    float2 tw[9];
+    if (s1) {
+#pragma unroll
+        for (int n2 = 0; n2 < 16; ++n2) hw[n2] = __ldg(g_hann + n1 + 25 * n2);
+#pragma unroll
+        for (int k2 = 1; k2 < 9; ++k2) tw[k2] = __ldg(g_tw + n1 * 9 + k2);
     }
+    pdl_wait();                                           // PCM / descriptors may come from the previous kernel
+    __syncthreads();
 
-    // ---- stage 1: 25 real 16-point DFTs per frame + twiddle -----------------------------------
-    // (window and twiddles are fetched while the sample loads are in flight)
-    {
-        const bool s1 = tid < kS1Frames * 25;
-        const int fi = tid / 25, n1 = tid - fi * 25;
-        float hw[16];
-        float2 tw[9];
-        if (s1) {
-#pragma unroll
-            for (int n2 = 0; n2 < 16; ++n2) hw[n2] = __ldg(g_hann + n1 + 25 * n2);
-#pragma unroll
-            for (int k2 = 1; k2 < 9; ++k2) tw[k2] = __ldg(g_tw + n1 * 9 + k2);
+    auto prefetch = [&](const MelTile& t, int buf) {     // tid 0 only; t.interior
+        const uint32_t bar = buf ? bar1 : bar0;
+        tc::fence_proxy_async();                          // the buffer was last touched through the generic proxy
+        tc::mbar_arrive_expect_tx(bar, kTileSamples * 4);
+        const float* src = pcm_base + t.pcm_off + (t.f0 * kHop - kPad);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(tc::smem_u32(s.u[buf])), "l"(src), "r"(kTileSamples * 4), "r"(bar) : "memory");
+    };
+
+    int tile = blockIdx.x;
+    if (tile >= n_tiles) return;
+    MelTile t = mel_tile_of(clips, n_clips, tile);
+    if (tid == 0 && t.interior) prefetch(t, 0);
+    uint32_t ph0 = 0, ph1 = 0;
+
+    for (int it = 0; tile < n_tiles; ++it) {
+        const int cur = it & 1;
+        float* u = s.u[cur];
+        const int f0 = t.f0, n_valid = t.n_valid;
+        const int next_tile = tile + gridDim.x;
+        MelTile tn = t;
+        if (next_tile < n_tiles) {
+            tn = mel_tile_of(clips, n_clips, next_tile);
+            if (tid == 0 && tn.interior) prefetch(tn, cur ^ 1);
         }
-        __syncthreads();
+        // ---- this tile's samples ---------------------------------------------------------------------
+        if (t.interior) {
+            if (cur) { tc::mbar_wait(bar1, ph1); ph1 ^= 1; } else { tc::mbar_wait(bar0, ph0); ph0 ^= 1; }
+        } else {
+            const float* __restrict__ pcm = pcm_base + t.pcm_off;
+            const int p0 = f0 * kHop;
+            const int need = (n_valid - 1) * kHop + kNFft;        // samples the valid frames touch
+            for (int i = tid; i < kTileSamples; i += kMelThreads)
+                u[i] = (i < need) ? padded_sample(pcm, t.n, p0 + i) : 0.0f;
+            __syncthreads();
+        }
+
+        // ---- stage 1: 25 real 16-point DFTs per frame + twiddle -----------------------------------
         if (s1) {
 #pragma unroll 1
             for (int f = fi; f < n_valid; f += kS1Frames) {
                 float x[16];
-                const float* xs = s.u + f * kHop + n1;
+                const float* xs = u + f * kHop + n1;
 #pragma unroll
                 for (int n2 = 0; n2 < 16; ++n2) x[n2] = xs[25 * n2] * hw[n2];
                 fft::cpx y[9];
@@ -141,76 +182,78 @@ mel_frames_kernel(const float* __restrict__ pcm_base, const MelClipDesc* __restr
                 }
             }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // ---- stage 2: 9 complex 25-point DFTs per frame -> power spectrum, stored [bin][frame] -------
-    {
-        const int f = tid & 31, k2 = tid >> 5;            // warp = k2, lane = frame: both smem sides conflict-free
-        if (f < n_valid) {
-            fft::cpx a[25];
+        // ---- stage 2: 9 complex 25-point DFTs per frame -> power spectrum, stored [bin][frame] -------
+        {
+            const int f = tid & 31, k2 = tid >> 5;            // warp = k2, lane = frame: both smem sides conflict-free
+            if (f < n_valid) {
+                fft::cpx a[25];
 #pragma unroll
-            for (int i = 0; i < 25; ++i) { float2 v = s.z[f][k2][i]; a[i] = fft::mk(v.x, v.y); }
-            fft::dft25(a);
-            // bin k = k2 + 16 k1 is direct for k1 <= 12 (k <= 200) and the mirror 400-k otherwise.  Mirrors go
-            // first: for k2 = 0 and 8 they land on bins this same thread also computes directly, and the
-            // direct value must win (program order within the thread); for other k2 they are unique.
-            float* pw = s.u + f;
+                for (int i = 0; i < 25; ++i) { float2 v = s.z[f][k2][i]; a[i] = fft::mk(v.x, v.y); }
+                fft::dft25(a);
+                // bin k = k2 + 16 k1 is direct for k1 <= 12 (k <= 200) and the mirror 400-k otherwise.  Mirrors go
+                // first: for k2 = 0 and 8 they land on bins this same thread also computes directly, and the
+                // direct value must win (program order within the thread); for other k2 they are unique.
+                float* pw = u + f;
 #pragma unroll
-            for (int k1 = 13; k1 < 25; ++k1)
-                pw[(400 - 16 * k1 - k2) * kFT] = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
+                for (int k1 = 13; k1 < 25; ++k1)
+                    pw[(400 - 16 * k1 - k2) * kFT] = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
 #pragma unroll
-            for (int k1 = 0; k1 < 13; ++k1)
-                pw[(16 * k1 + k2) * kFT] = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
+                for (int k1 = 0; k1 < 13; ++k1)
+                    pw[(16 * k1 + k2) * kFT] = a[k1].re * a[k1].re + a[k1].im * a[k1].im;
+            }
         }
-    }
-    __syncthreads();
+        __syncthreads();
 
-    // ---- stage 3: filterbank, log10, store, running max ----------------------------------------
-    float vmax = -INFINITY;
-    {
-        const int q = tid & 7;                            // frames 4q .. 4q+3 of the tile
-        float* __restrict__ out = mel_base + cd.mel_off;
-        const bool vec_ok = ((cd.n_len & 3) | (int)(reinterpret_cast<uintptr_t>(out) & 15)) == 0;   // rows stay 16-byte aligned
-        const float4* pw4 = reinterpret_cast<const float4*>(s.u) + q;
-        if (4 * q < n_valid) {
-            for (int m = tid >> 3; m < n_mel; m += kMelThreads / 8) {
-                const int b0 = b0tab[m], w0 = ptab[m], w1 = ptab[m + 1];
-                float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                const float4* pp = pw4 + b0 * (kFT / 4);
+        // ---- stage 3: filterbank, log10, store, running max ----------------------------------------
+        float vmax = -INFINITY;
+        {
+            const int q = tid & 7;                            // frames 4q .. 4q+3 of the tile
+            float* __restrict__ out = mel_base + t.mel_off;
+            const bool vec_ok = ((t.n_len & 3) | (int)(reinterpret_cast<uintptr_t>(out) & 15)) == 0;   // rows stay 16-byte aligned
+            const float4* pw4 = reinterpret_cast<const float4*>(u) + q;
+            if (4 * q < n_valid) {
+                for (int m = tid >> 3; m < n_mel; m += kMelThreads / 8) {
+                    const int b0 = b0tab[m], w0 = ptab[m], w1 = ptab[m + 1];
+                    float4 acc = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    const float4* pp = pw4 + b0 * (kFT / 4);
 #pragma unroll 4
-                for (int j = w0; j < w1; ++j) {
-                    const float w = wtab[j];
-                    const float4 p = pp[(j - w0) * (kFT / 4)];
-                    acc.x = fmaf(w, p.x, acc.x); acc.y = fmaf(w, p.y, acc.y);
-                    acc.z = fmaf(w, p.z, acc.z); acc.w = fmaf(w, p.w, acc.w);
-                }
-                const float kLog10Of2 = 0.30102999566398120f;
-                float4 v;
-                v.x = __log2f(fmaxf(acc.x, 1e-10f)) * kLog10Of2; v.y = __log2f(fmaxf(acc.y, 1e-10f)) * kLog10Of2;
-                v.z = __log2f(fmaxf(acc.z, 1e-10f)) * kLog10Of2; v.w = __log2f(fmaxf(acc.w, 1e-10f)) * kLog10Of2;
-                float* dst = out + (long long)m * cd.n_len + f0 + 4 * q;
-                const int left = n_valid - 4 * q;         // >= 1
-                if (left >= 4 && vec_ok) {
-                    *reinterpret_cast<float4*>(dst) = v;
-                    vmax = fmaxf(vmax, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
-                } else {
-                    dst[0] = v.x; vmax = fmaxf(vmax, v.x);
-                    if (left > 1) { dst[1] = v.y; vmax = fmaxf(vmax, v.y); }
-                    if (left > 2) { dst[2] = v.z; vmax = fmaxf(vmax, v.z); }
-                    if (left > 3) { dst[3] = v.w; vmax = fmaxf(vmax, v.w); }
+                    for (int j = w0; j < w1; ++j) {
+                        const float w = wtab[j];
+                        const float4 p = pp[(j - w0) * (kFT / 4)];
+                        acc.x = fmaf(w, p.x, acc.x); acc.y = fmaf(w, p.y, acc.y);
+                        acc.z = fmaf(w, p.z, acc.z); acc.w = fmaf(w, p.w, acc.w);
+                    }
+                    const float kLog10Of2 = 0.30102999566398120f;
+                    float4 v;
+                    v.x = __log2f(fmaxf(acc.x, 1e-10f)) * kLog10Of2; v.y = __log2f(fmaxf(acc.y, 1e-10f)) * kLog10Of2;
+                    v.z = __log2f(fmaxf(acc.z, 1e-10f)) * kLog10Of2; v.w = __log2f(fmaxf(acc.w, 1e-10f)) * kLog10Of2;
+                    float* dst = out + (long long)m * t.n_len + f0 + 4 * q;
+                    const int left = n_valid - 4 * q;         // >= 1
+                    if (left >= 4 && vec_ok) {
+                        *reinterpret_cast<float4*>(dst) = v;
+                        vmax = fmaxf(vmax, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+                    } else {
+                        dst[0] = v.x; vmax = fmaxf(vmax, v.x);
+                        if (left > 1) { dst[1] = v.y; vmax = fmaxf(vmax, v.y); }
+                        if (left > 2) { dst[2] = v.z; vmax = fmaxf(vmax, v.z); }
+                        if (left > 3) { dst[3] = v.w; vmax = fmaxf(vmax, v.w); }
+                    }
                 }
             }
         }
-    }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
-    if ((tid & 31) == 0) s.red[tid >> 5] = vmax;
-    __syncthreads();
-    if (tid == 0) {
-        float v = s.red[0];
-        for (int w = 1; w < kMelThreads / 32; ++w) v = fmaxf(v, s.red[w]);
-        if (v > -INFINITY) atomicMax(clip_max + lo, ordered_from_float(v));
+        for (int o = 16; o > 0; o >>= 1) vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o));
+        if ((tid & 31) == 0) s.red[tid >> 5] = vmax;
+        __syncthreads();                                  // also: every thread is done with u (power) and z
+        if (tid == 0) {
+            float v = s.red[0];
+            for (int w = 1; w < kMelThreads / 32; ++w) v = fmaxf(v, s.red[w]);
+            if (v > -INFINITY) atomicMax(clip_max + t.clip, ordered_from_float(v));
+        }
+        tile = next_tile;
+        t = tn;
     }
 }
 
@@ -307,8 +350,9 @@ int mel_launch(q3a_frontend* fe, const float* pcm_dev, const int64_t* pcm_off, c
     const MelClipDesc* d_desc = fe->desc.as<MelClipDesc>();
     unsigned* d_max = fe->maxbuf.as<unsigned>();
     if (tiles > 0) {
-        Q3A_CUDA(launch_pdl(mel_frames_kernel, dim3(tiles), dim3(kMelThreads), sizeof(MelSmem), stream,
-                            pcm_dev, d_desc, n_clips, (const float*)fe->d_hann, (const float2*)fe->d_twiddle,
+        const int grid = tiles < 2 * fe->n_sms ? tiles : 2 * fe->n_sms;     // persistent: two CTAs per SM
+        Q3A_CUDA(launch_pdl(mel_frames_kernel, dim3(grid), dim3(kMelThreads), sizeof(MelSmem), stream,
+                            pcm_dev, d_desc, n_clips, tiles, (const float*)fe->d_hann, (const float2*)fe->d_twiddle,
                             (const int*)fe->d_row_bin0, (const int*)fe->d_row_ptr, (const float*)fe->d_weights, fe->n_mel,
                             mel_dev, d_max));
         ++g_launch_counter;
@@ -392,6 +436,7 @@ extern "C" int q3a_frontend_create(int device, const float* filters, int n_mel, 
 
     q3a_frontend* fe = new q3a_frontend();
     fe->device = device; fe->n_mel = n_mel; fe->n_bins = n_bins;
+    if (cudaDeviceGetAttribute(&fe->n_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || fe->n_sms <= 0) fe->n_sms = 148;
     auto fail = [&](int rc) { q3a_frontend_free(fe); return rc; };
 #define FE_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error(std::string(#x) + ": " + cudaGetErrorString(e_)); return fail(Q3A_ERR_CUDA); } } while (0)
     FE_CUDA(cudaMalloc(&fe->d_hann, sizeof(float) * kNFft));

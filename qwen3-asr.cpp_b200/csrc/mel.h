@@ -6,6 +6,7 @@ struct q3a_frontend {
     int device = 0;
     int n_mel = 128;
     int n_bins = 201;
+    int n_sms = 148;                // persistent grid of mel_frames_kernel = 2 CTAs per SM
     // resident tables
     float* d_hann = nullptr;        // [400] periodic Hann, float(double value) (mel_spectrogram.cpp:28-58)
     float2* d_twiddle = nullptr;    // [25][9]  W400^(n1*k2)
