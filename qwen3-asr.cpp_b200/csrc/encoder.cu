@@ -697,8 +697,8 @@ static void plan_passes(const int* n_frames, int n, int mode, std::vector<int>& 
     bounds.push_back(n);
 }
 
-// Cuts [0, n) into at most `parts` runs of roughly equal weight.
-static std::vector<int> balanced_split(const std::vector<long long>& weight, int parts) {
+// Cuts [0, n) into at most `parts` runs whose cumulative weight follows `frac` (ascending, last = 1).
+static std::vector<int> weighted_split(const std::vector<long long>& weight, int parts, const double* frac) {
     const int n = (int)weight.size();
     long long total = 0;
     for (long long w : weight) total += w;
@@ -707,11 +707,15 @@ static std::vector<int> balanced_split(const std::vector<long long>& weight, int
     for (int i = 0; i < n; ++i) {
         acc += weight[i];
         const int k = (int)sp.size();                       // next boundary to place
-        if (k < parts && i + 1 < n && acc * parts >= total * k) sp.push_back(i + 1);
+        if (k < parts && i + 1 < n && (double)acc >= frac[k - 1] * (double)total) sp.push_back(i + 1);
     }
     sp.push_back(n);
     return sp;
 }
+// uploads: a small first part (only its copy is exposed), then equal parts; downloads: halves
+static const double kInFrac[4] = {0.10, 0.40, 0.70, 1.0};
+static const double kOutFrac[2] = {0.5, 1.0};
+static const double kOne[1] = {1.0};
 
 // The pipeline itself.  `in[i]` has `in_elems[i]` floats on the host; `compute(u0, nu, in_dev, in_off, out_dev,
 // hooks)` enqueues the pass on e->stream.  Inside a pass the upload is cut into kInParts and the download into
@@ -749,8 +753,9 @@ static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in
             T += w_out[i];
         }
         const long long in_bytes = 4ll * ioff[p][nu], out_bytes = 4ll * T * width;
-        in_split[p] = balanced_split(w_in, split_ok && in_bytes >= kSplitMinBytes ? q3a_encoder::kInParts : 1);
-        out_split[p] = balanced_split(w_out, split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY ? q3a_encoder::kOutParts : 1);
+        in_split[p] = split_ok && in_bytes >= kSplitMinBytes ? weighted_split(w_in, q3a_encoder::kInParts, kInFrac) : weighted_split(w_in, 1, kOne);
+        out_split[p] = split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY ? weighted_split(w_out, q3a_encoder::kOutParts, kOutFrac)
+                                                                                               : weighted_split(w_out, 1, kOne);
         need_in[p & 1] = std::max(need_in[p & 1], sizeof(float) * (size_t)(ioff[p][nu] + 64));
         need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)T * width + 64));
     }

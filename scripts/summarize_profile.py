@@ -41,35 +41,58 @@ def short_name(full: str) -> str:
 
 
 def launches(tag: str) -> None:
+    """gpurun_out/launches.csv: one ncu pass over the launches of ONE bench step with
+    --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --print-units base."""
     path = os.path.join(GO, "launches.csv")
     if not os.path.exists(path):
         return
     rows = list(csv.reader(open(path, newline="")))
     hi = next(i for i, r in enumerate(rows) if r and r[0] == "ID")
     hdr = rows[hi]
-    kn, mv, gs, bs = hdr.index("Kernel Name"), hdr.index("Metric Value"), hdr.index("Grid Size"), hdr.index("Block Size")
+    kn, mn, mv = hdr.index("Kernel Name"), hdr.index("Metric Name"), hdr.index("Metric Value")
+    gs, bs, idc = hdr.index("Grid Size"), hdr.index("Block Size"), hdr.index("ID")
+    per_launch: dict = collections.OrderedDict()
+    for r in rows[hi + 1:]:
+        if len(r) <= mv or not r[idc].isdigit():
+            continue
+        d = per_launch.setdefault(r[idc], {"key": (short_name(r[kn]), r[gs], r[bs])})
+        try:
+            d[r[mn]] = float(r[mv].replace(",", ""))
+        except ValueError:
+            pass
     agg: dict = collections.OrderedDict()
     total = 0.0
-    n = 0
-    for r in rows[hi + 1:]:
-        if len(r) <= mv:
-            continue
-        ns = float(r[mv].replace(",", ""))
-        key = (short_name(r[kn]), r[gs], r[bs])
-        a = agg.setdefault(key, [0, 0.0])
+    for d in per_launch.values():
+        a = agg.setdefault(d["key"], [0, 0.0, 0.0])
         a[0] += 1
-        a[1] += ns
-        total += ns
-        n += 1
+        a[1] += d.get("gpu__time_duration.sum", 0.0)
+        a[2] += d.get("dram__bytes_read.sum", 0.0) + d.get("dram__bytes_write.sum", 0.0)
+        total += d.get("gpu__time_duration.sum", 0.0)
+    n = len(per_launch)
     with open(os.path.join(PROF, f"{tag}_launches.md"), "w") as f:
         f.write(f"# ncu launch list — {tag}\n\n")
-        f.write("`ncu --metrics gpu__time_duration.sum --clock-control none` over whole steps of `bench.py` "
-                "(64 x 30-s clips, ASR-0.6B, bf16 operands).  Times are cold-cache and serialised: compare shares.\n\n")
+        f.write("`ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none` over one "
+                "step of `bench.py` (64 x 30-s clips, ASR-0.6B, bf16 operands).  Times are cold-cache and serialised: "
+                "compare shares.  DRAM = read + write bytes of all launches of the row.\n\n")
         f.write(f"{n} launches, {total / 1e6:.3f} ms in total.\n\n")
-        f.write("| kernel | grid | block | launches | total ms | share | mean us |\n|---|---|---|---:|---:|---:|---:|\n")
-        for (name, g, b), (cnt, ns) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-            f.write(f"| `{name}` | {g} | {b} | {cnt} | {ns / 1e6:.3f} | {100 * ns / total:.1f}% | {ns / cnt / 1e3:.1f} |\n")
-    print("wrote", f"profiles/{tag}_launches.md")
+        f.write("| kernel | grid | block | launches | total ms | share | mean us | DRAM MB | GB/s |\n|---|---|---|---:|---:|---:|---:|---:|---:|\n")
+        for (name, g, b), (cnt, ns, by) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write(f"| `{name}` | {g} | {b} | {cnt} | {ns / 1e6:.3f} | {100 * ns / total:.1f}% | {ns / cnt / 1e3:.1f} | "
+                    f"{by / 1e6:.1f} | {by / max(ns, 1.0):.0f} |\n")
+    traffic = {}
+    for (name, g, b), (cnt, ns, by) in agg.items():
+        fam = name.split("<")[0]
+        t = traffic.setdefault(fam, {"launches": 0, "dram_bytes": 0.0, "ns": 0.0})
+        t["launches"] += cnt; t["dram_bytes"] += by; t["ns"] += ns
+    with open(os.path.join(PROF, f"{tag}_traffic.json"), "w") as f:
+        json.dump({"source": f"profiles/{tag}_launches.md (ncu dram__bytes_read.sum + dram__bytes_write.sum, one bench step)",
+                   "kernels": traffic}, f, indent=1)
+    g = traffic.get("gemm_tc_kernel")
+    if g and g["launches"] and g["dram_bytes"] > 0:
+        with open(os.path.join(PROF, "roofline_traffic.json"), "w") as f:       # read by bench.py -> roofline.traffic
+            json.dump({"gemm_tc_kernel_dram_bytes_per_launch": g["dram_bytes"] / g["launches"], "launches_per_step": g["launches"],
+                       "source": f"profiles/{tag}_traffic.json"}, f, indent=1)
+    print("wrote", f"profiles/{tag}_launches.md", f"profiles/{tag}_traffic.json")
 
 
 def full_reports(tag: str) -> None:
