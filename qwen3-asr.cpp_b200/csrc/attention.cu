@@ -6,19 +6,22 @@
 // utterance for the ASR encoder (no mask), 104-token windows for the aligner.  Scores are never
 // written to HBM.
 //
-// One CTA (128 threads, one query row per thread, two CTAs per SM) = one (128-query tile, head).
-// Per 128-key block j:
-//   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,128); issued one block ahead, so it runs
+// One CTA (128 threads, one query row per thread) = one (128-query tile, head); keys go in blocks of KT = 64
+// (three CTAs per SM; KT = 128 with two CTAs per SM is kept behind Q3A_ATTN_KT=128).
+// Per key block j:
+//   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,KT); issued one block ahead, so it runs
 //                            while the threads are still busy with block j-1
-//   S_j -> registers         four tcgen05.ld.x32 back to back, one wait
-//   softmax                  row maximum, p = exp2(s*scale - m) with a lazily updated reference maximum m
-//                            (O in TMEM is rescaled only when the row maximum grows by more than 2^8, so the
-//                            common block never reads O back), row sum in fp32
+//   S_j -> registers         tcgen05.ld.x32 back to back, one wait
+//   softmax                  row maximum (four chains), p = exp2(s*scale - m) with a lazily updated reference
+//                            maximum m (O in TMEM is rescaled only when the row maximum grows by more than 2^8,
+//                            so the common block never reads O back), row sum in fp32, P packed in place
 //   P_j -> smem (16-bit, 128-byte swizzled K-major), O += P_j V_j   tcgen05.mma accumulating in TMEM
-//                            columns [128,192); V is the MN-major B operand
+//                            columns [KT,KT+64); V is the MN-major B operand
 // K and V blocks are double-buffered with separate barriers: K_{j+2} is fetched as soon as Q K_j^T has
-// retired, V_{j+1} as soon as P_{j-1} V_{j-1} has.  Warps whose 32 query rows all lie past the end of the
-// segment skip the softmax arithmetic.  The epilogue divides by the row sum and stores 16-bit rows.
+// retired, V_{j+1} as soon as P_{j-1} V_{j-1} has.  Warp 0 doubles as the issue warp and stays converged
+// (elect.sync around the TMA / MMA instructions only).  Warps whose 32 query rows all lie past the end of the
+// segment skip the softmax arithmetic.  The epilogue divides by the row sum, transposes through the idle Q tile
+// and stores whole 128-byte rows.  DESIGN.md 4.2 has the measurements behind each of these choices.
 #include "attention.h"
 #include "tc.cuh"
 #include "tmap.h"
@@ -291,26 +294,33 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     // ---- epilogue: O / l -> 16-bit rows ---------------------------------------------------------------
     tc::mbar_wait(bar_o, (nkv - 1) & 1);
     tc::fence_after_sync();
-    const int row = t.q0 + tid;
+    // O / l is packed to 16 bits, staged through the (now idle) Q tile with the usual 16-byte XOR swizzle and
+    // written out by each warp for its own 32 rows with 8 lanes per row: every store instruction covers four
+    // whole 128-byte rows instead of 32 row fragments.
     if (row_live) {
         const float inv = 1.0f / l_run;
-        OpT* dst = out + (size_t)row * d_model + head * kHd;
+        uint32_t r[64];
+        tc::tmem_ld_32x32b_x32(t_row + kKT, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
+        tc::tmem_ld_32x32b_x32(t_row + kKT + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
+        tc::tmem_ld_wait();
+        uint8_t* stage = smem_raw + tid * 128;
 #pragma unroll
-        for (int c = 0; c < kHd; c += 32) {
-            uint32_t r[32];
-            tc::tmem_ld_32x32b_x32(t_row + kKT + c, r);
-            tc::tmem_ld_wait();
-            if (row < t.seg_end) {
+        for (int g = 0; g < 8; ++g) {
+            uint4 u;
+            u.x = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
+            u.y = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
+            u.z = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
+            u.w = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+            *reinterpret_cast<uint4*>(stage + ((g ^ (tid & 7)) << 4)) = u;
+        }
+        __syncwarp();
+        const int lane = tid & 31, sub = lane >> 3, g = lane & 7;
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    uint4 u;
-                    u.x = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
-                    u.y = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
-                    u.z = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
-                    u.w = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
-                    *reinterpret_cast<uint4*>(dst + c + g * 8) = u;
-                }
-            }
+        for (int i = 0; i < 8; ++i) {
+            const int rr = warp * 32 + i * 4 + sub;                 // row of the tile
+            const uint4 u = *reinterpret_cast<const uint4*>(smem_raw + rr * 128 + ((g ^ (rr & 7)) << 4));
+            if (t.q0 + rr < t.seg_end)
+                *reinterpret_cast<uint4*>(out + (size_t)(t.q0 + rr) * d_model + head * kHd + g * 8) = u;
         }
     }
     tc::fence_before_sync();
