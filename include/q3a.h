@@ -149,6 +149,12 @@ int q3a_encoder_encode_device(q3a_encoder* enc, const float* mel_dev, const int6
  * (qwen3_asr.cpp:90,105) / ForcedAligner::align's (forced_aligner.cpp:1653,1661) for a batch. */
 int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* enc, const float* const* pcm, const int* n_samples,
                          int n_clips, int mode, float* const* out, int* n_tokens);
+/* same from 16-bit PCM as it sits in a WAV file: load_wav's conversion (mel_spectrogram.cpp:195-210: interleaved
+ * channels averaged in float, then / 32768) runs on the device, so the upload is 2 bytes per sample.  n_samples[i]
+ * counts frames (samples per channel); pcm[i] holds n_samples[i] * n_channels values; n_channels in 1..8.
+ * Results are bit-identical to q3a_encode_pcm_batch on load_wav's float output. */
+int q3a_encode_pcm16_batch(q3a_frontend* fe, q3a_encoder* enc, const int16_t* const* pcm, const int* n_samples,
+                           int n_channels, int n_clips, int mode, float* const* out, int* n_tokens);
 /* same with PCM and features resident on the device (packed as above). */
 int q3a_encode_pcm_device(q3a_frontend* fe, q3a_encoder* enc, const float* pcm_dev, const int64_t* pcm_off,
                           const int* n_samples, int n_clips, int mode, float* out_dev, int64_t* tok_off,

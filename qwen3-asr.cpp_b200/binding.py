@@ -58,6 +58,7 @@ SYMBOLS = {
     "q3a_encoder_encode_batch": (_I, [_P, _P, _I, _P, _I, _I, _P, _P]),
     "q3a_encoder_encode_device": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
     "q3a_encode_pcm_batch": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
+    "q3a_encode_pcm16_batch": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
     "q3a_encode_pcm_device": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
     "q3a_encoder_set_profiling": (_I, [_P, _I]),
     "q3a_encoder_get_timings": (_I, [_P, C.POINTER(Timings)]),
@@ -203,6 +204,17 @@ class Encoder:
         n_tok = (C.c_int * len(clips))()
         check(self.lib.q3a_encode_pcm_batch(fe.h, self.h, _ptr_array(clips), _int_array(n), len(clips), mode,
                                             _ptr_array(outs), n_tok))
+        return outs
+
+    def encode_pcm16_batch(self, fe: Frontend, clips: list[np.ndarray], n_channels: int = 1,
+                           mode: int = MODE_ASR) -> list[np.ndarray]:
+        """clips: int16 arrays of n_frames * n_channels interleaved samples (a WAV file's data chunk)"""
+        clips = [np.ascontiguousarray(c, dtype=np.int16).reshape(-1) for c in clips]
+        n = [len(c) // n_channels for c in clips]
+        outs = [np.zeros((max(self.n_tokens(k // 160, mode), 0), self.out_width(mode)), dtype=np.float32) for k in n]
+        n_tok = (C.c_int * len(clips))()
+        check(self.lib.q3a_encode_pcm16_batch(fe.h, self.h, _ptr_array(clips), _int_array(n), n_channels, len(clips), mode,
+                                              _ptr_array(outs), n_tok))
         return outs
 
     def encode_pcm_device(self, fe: Frontend, pcm_ptr: int, pcm_off, n_samples, out_ptr: int, mode: int = MODE_ASR,

@@ -567,7 +567,7 @@ extern "C" void q3a_encoder_free(q3a_encoder* e) {
     e->arena.release(); e->pe.release();
     e->planes1.release(); e->planes2.release(); e->feat.release(); e->x.release(); e->h.release(); e->qkv.release();
     e->att.release(); e->up.release(); e->tables.release(); e->stage_in.release(); e->stage_out.release();
-    e->stage_in2.release(); e->stage_out2.release();
+    e->stage_in2.release(); e->stage_out2.release(); e->stage_pcm.release();
     e->stage_mel.release(); e->stage_max.release();
     e->ring.release();
     for (auto ev : e->ev_pool) cudaEventDestroy(ev);
@@ -643,7 +643,7 @@ extern "C" int q3a_encoder_get_timings(const q3a_encoder* e, q3a_timings* out) {
 extern "C" int64_t q3a_encoder_device_bytes(const q3a_encoder* e) {
     if (!e) return 0;
     return (int64_t)(e->arena.cap + e->pe.cap + e->planes1.cap + e->planes2.cap + e->feat.cap + e->x.cap + e->h.cap +
-                     e->qkv.cap + e->att.cap + e->up.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap + e->stage_in2.cap + e->stage_out2.cap +
+                     e->qkv.cap + e->att.cap + e->up.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap + e->stage_in2.cap + e->stage_out2.cap + e->stage_pcm.cap +
                      e->stage_mel.cap + e->stage_max.cap);
 }
 
@@ -724,8 +724,8 @@ static const double kOne[1] = {1.0};
 constexpr long long kSplitMinBytes = 16ll << 20;
 
 template <class Compute>
-static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in_elems, const int* n_frames, int n,
-                           int mode, int width, float* const* out, int* n_tokens, Compute compute) {
+static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_elems, int elem_bytes, int64_t align_elems,
+                           const int* n_frames, int n, int mode, int width, float* const* out, int* n_tokens, Compute compute) {
     static const bool trace = getenv("Q3A_TRACE") != nullptr;
     const auto t_begin = std::chrono::steady_clock::now();
     auto stamp = [&](const char* what) {
@@ -744,7 +744,7 @@ static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in
     const bool split_ok = getenv("Q3A_NO_PART_OVERLAP") == nullptr;
     for (int p = 0; p < n_pass; ++p) {
         const int u0 = bounds[p], nu = bounds[p + 1] - u0;
-        q3a_pack_offsets(in_elems + u0, nu, 1, 64, ioff[p]);
+        q3a_pack_offsets(in_elems + u0, nu, 1, align_elems, ioff[p]);
         std::vector<long long> w_in(nu), w_out(nu);
         long long T = 0;
         for (int i = 0; i < nu; ++i) {
@@ -752,11 +752,11 @@ static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in
             w_out[i] = encoder_n_tokens(n_frames[u0 + i], mode);
             T += w_out[i];
         }
-        const long long in_bytes = 4ll * ioff[p][nu], out_bytes = 4ll * T * width;
+        const long long in_bytes = (long long)elem_bytes * ioff[p][nu], out_bytes = 4ll * T * width;
         in_split[p] = split_ok && in_bytes >= kSplitMinBytes ? weighted_split(w_in, q3a_encoder::kInParts, kInFrac) : weighted_split(w_in, 1, kOne);
         out_split[p] = split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY ? weighted_split(w_out, q3a_encoder::kOutParts, kOutFrac)
                                                                                                : weighted_split(w_out, 1, kOne);
-        need_in[p & 1] = std::max(need_in[p & 1], sizeof(float) * (size_t)(ioff[p][nu] + 64));
+        need_in[p & 1] = std::max(need_in[p & 1], (size_t)elem_bytes * (size_t)(ioff[p][nu] + align_elems));
         need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)T * width + 64));
     }
     for (int b = 0; b < 2; ++b) {
@@ -776,8 +776,8 @@ static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in
         for (size_t part = 0; part + 1 < sp.size(); ++part) {
             for (int i = sp[part]; i < sp[part + 1]; ++i)
                 if (in_elems[u0 + i] > 0)
-                    PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<float>() + ioff[p][i], in[u0 + i], sizeof(float) * in_elems[u0 + i],
-                                              cudaMemcpyHostToDevice, e->copy_in));
+                    PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<uint8_t>() + (size_t)elem_bytes * ioff[p][i], in[u0 + i],
+                                              (size_t)elem_bytes * in_elems[u0 + i], cudaMemcpyHostToDevice, e->copy_in));
             PIPE_CUDA(cudaEventRecord(e->ev_part_in[b][part], e->copy_in));
         }
         return Q3A_OK;
@@ -809,7 +809,7 @@ static int run_host_passes(q3a_encoder* e, const float* const* in, const int* in
             }
             return Q3A_OK;
         };
-        const int rc = compute(u0, nu, sin[b]->as<float>(), ioff[p].data(), sout[b]->as<float>(), &hk);
+        const int rc = compute(u0, nu, sin[b]->p, ioff[p].data(), sout[b]->as<float>(), &hk);
         if (rc != Q3A_OK) return drain(rc);
         stamp("compute enqueued");
         PIPE_CUDA(cudaEventRecord(e->ev_comp[b], e->stream));
@@ -841,9 +841,9 @@ extern "C" int q3a_encoder_encode_batch(q3a_encoder* e, const float* const* mel,
     const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
     std::vector<int> elems(n_utts);
     for (int i = 0; i < n_utts; ++i) elems[i] = n_mel * n_frames[i];
-    Q3A_TRY(run_host_passes(e, mel, elems.data(), n_frames, n_utts, mode, width, out, n_tokens,
-                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
-                                return encode_dispatch(e, in_dev, in_off, nullptr, n_frames + u0, nu, mode, out_dev, nullptr, e->stream, hk);
+    Q3A_TRY(run_host_passes(e, reinterpret_cast<const void* const*>(mel), elems.data(), 4, 64, n_frames, n_utts, mode, width, out, n_tokens,
+                            [&](int u0, int nu, const void* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
+                                return encode_dispatch(e, static_cast<const float*>(in_dev), in_off, nullptr, n_frames + u0, nu, mode, out_dev, nullptr, e->stream, hk);
                             }));
     return prof_collect(e, e->stream);
 }
@@ -911,9 +911,70 @@ extern "C" int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* e, const floa
     const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
     std::vector<int> nf(n_clips);
     for (int i = 0; i < n_clips; ++i) nf[i] = n_samples[i] / 160;
-    Q3A_TRY(run_host_passes(e, pcm, n_samples, nf.data(), n_clips, mode, width, out, n_tokens,
-                            [&](int u0, int nu, const float* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
-                                return pcm_core(fe, e, in_dev, in_off, n_samples + u0, nu, mode, out_dev, nullptr, e->stream, hk);
+    Q3A_TRY(run_host_passes(e, reinterpret_cast<const void* const*>(pcm), n_samples, 4, 64, nf.data(), n_clips, mode, width, out, n_tokens,
+                            [&](int u0, int nu, const void* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
+                                return pcm_core(fe, e, static_cast<const float*>(in_dev), in_off, n_samples + u0, nu, mode, out_dev, nullptr, e->stream, hk);
+                            }));
+    return prof_collect(e, e->stream);
+}
+
+// int16 ingest: load_wav's conversion (mel_spectrogram.cpp:195-210) on the device, so the upload carries 2 bytes per
+// sample instead of 4.  One launch per upload part: frame f of the packed mono buffer = average of the n_channels
+// interleaved samples (float sum / n_channels, the reference's operation order) / 32768.
+__global__ void __launch_bounds__(256)
+pcm16_to_f32_kernel(const int16_t* __restrict__ in, float* __restrict__ out, long long n_frames, int n_channels) {
+    pdl_trigger();
+    pdl_wait();
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long f = (long long)blockIdx.x * blockDim.x + threadIdx.x; f < n_frames; f += stride) {
+        float v;
+        if (n_channels == 1) {
+            v = (float)in[f] / 32768.0f;
+        } else {
+            float sum = 0.0f;
+            for (int c = 0; c < n_channels; ++c) sum += (float)in[f * n_channels + c];
+            v = (sum / (float)n_channels) / 32768.0f;
+        }
+        out[f] = v;
+    }
+}
+
+extern "C" int q3a_encode_pcm16_batch(q3a_frontend* fe, q3a_encoder* e, const int16_t* const* pcm, const int* n_samples,
+                                      int n_channels, int n_clips, int mode, float* const* out, int* n_tokens) {
+    if (!e || !fe) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
+    if (n_channels < 1 || n_channels > 8) { set_error("encode_pcm16_batch: n_channels must be 1..8"); return Q3A_ERR_ARG; }
+    if (n_clips < 0 || (n_clips > 0 && (!pcm || !n_samples || !out))) { set_error("encode_pcm16_batch: null argument"); return Q3A_ERR_ARG; }
+    for (int u = 0; u < n_clips; ++u)
+        if (n_samples[u] < 0 || (n_samples[u] > 0 && !pcm[u]) || (n_samples[u] >= 160 && !out[u])) {
+            set_error("encode_pcm16_batch: bad clip " + std::to_string(u)); return Q3A_ERR_ARG;
+        }
+    Q3A_TRY(use_device(e->device));
+    g_launch_counter = 0;
+    prof_reset(e);
+    const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
+    std::vector<int> nf(n_clips), elems(n_clips);
+    for (int i = 0; i < n_clips; ++i) { nf[i] = n_samples[i] / 160; elems[i] = n_samples[i] * n_channels; }
+    // clips are packed at multiples of 64 frames, i.e. 64 * n_channels int16 elements: element offset = n_channels * frame offset
+    Q3A_TRY(run_host_passes(e, reinterpret_cast<const void* const*>(pcm), elems.data(), 2, 64ll * n_channels, nf.data(), n_clips, mode,
+                            width, out, n_tokens,
+                            [&](int u0, int nu, const void* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) -> int {
+                                std::vector<int64_t> foff(nu + 1);
+                                for (int i = 0; i <= nu; ++i) foff[i] = in_off[i] / n_channels;
+                                Q3A_TRY(e->stage_pcm.reserve(sizeof(float) * (size_t)(foff[nu] + 64)));
+                                float* mono = e->stage_pcm.as<float>();
+                                PartHooks mine = *hk;
+                                mine.before_stem = [&](int part, int ua, int ub) -> int {
+                                    if (hk->before_stem) Q3A_TRY(hk->before_stem(part, ua, ub));
+                                    const long long f0 = foff[ua], n = foff[ub] - foff[ua];
+                                    if (n <= 0) return Q3A_OK;
+                                    const int blocks = (int)std::min<long long>((n + 256 * 8 - 1) / (256 * 8), 148 * 8);
+                                    Q3A_CUDA(launch_pdl(pcm16_to_f32_kernel, dim3(blocks), dim3(256), 0, e->stream,
+                                                        static_cast<const int16_t*>(in_dev) + f0 * n_channels, mono + f0, n, n_channels));
+                                    ++g_launch_counter;
+                                    return Q3A_OK;
+                                };
+                                return pcm_core(fe, e, mono, foff.data(), n_samples + u0, nu, mode, out_dev, nullptr, e->stream, &mine);
                             }));
     return prof_collect(e, e->stream);
 }

@@ -182,6 +182,32 @@ def test_copy_overlap_partitions_do_not_change_results(lib, asr_model, monkeypat
     enc.close(); fe.close()
 
 
+def test_int16_ingest_matches_load_wav_conversion(lib, tiny_models):
+    """q3a_encode_pcm16_batch = load_wav's int16 -> float conversion (mel_spectrogram.cpp:195-210) + the float path:
+    mono and interleaved stereo, bit-identical to converting on the host the way the reference does."""
+    shape, models = tiny_models
+    path, _ = models["f16"]
+    enc = B.Encoder(path, 0, B.OP_F16)
+    fe = B.Frontend(0)
+    rng = np.random.default_rng(3)
+    lens = [16000 * 3 + 77, 160 * 7, 0, 16000 + 1, 159]
+    mono16 = [np.round(synth.synth_audio(900 + i, n) * 32767).astype(np.int16) for i, n in enumerate(lens)]
+    want = enc.encode_pcm_batch(fe, [c.astype(np.float32) / np.float32(32768.0) for c in mono16], B.MODE_ASR)
+    got = enc.encode_pcm16_batch(fe, mono16, 1, B.MODE_ASR)
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and np.array_equal(a, b)
+    stereo16 = [np.stack([c, rng.integers(-3000, 3000, len(c)).astype(np.int16)], axis=1) for c in mono16]
+    host = []
+    for c in stereo16:                                        # (sum / num_channels) / 32768.0f in float, as load_wav does
+        ssum = c[:, 0].astype(np.float32) + c[:, 1].astype(np.float32)
+        host.append((ssum / np.float32(2)) / np.float32(32768.0))
+    want = enc.encode_pcm_batch(fe, host, B.MODE_ASR)
+    got = enc.encode_pcm16_batch(fe, [c.reshape(-1) for c in stereo16], 2, B.MODE_ASR)
+    for a, b in zip(got, want):
+        assert a.shape == b.shape and np.array_equal(a, b)
+    enc.close(); fe.close()
+
+
 def test_aligner_shape_variable_length_batch(lib, filters, tmp_path):
     """BASELINE config 4 (reduced: 4 layers of the aligner width, 5-40 s utterances): padded-tail stem, 104-token windows"""
     shape = synth.EncoderShape("aligner-4l", 4, 1024, 16, 4096)
