@@ -17,7 +17,7 @@
 //                K-major row) into a 3-stage ring
 //   warp 4       TMEM allocator + MMA issuer: per tile two N-halves (256 + C-256 columns) = two accumulator
 //                buffers, so the epilogue of one half overlaps the MMAs of the next
-//   warps 5..12  epilogue: tcgen05.ld -> bias + GELU -> 16-bit -> smem staging -> TMA store
+//   warps 5..20  epilogue (four per TMEM lane quadrant, interleaved over the 32-channel chunks): tcgen05.ld -> bias + GELU -> 16-bit -> smem staging -> TMA store
 #include "stem.h"
 #include "tc.cuh"
 #include "tmap.h"
@@ -26,14 +26,15 @@
 
 namespace q3a {
 
-constexpr int kC1Threads = 13 * 32;
+constexpr int kC1EpiWarps = 16;                  // 4 per scheduler: the epilogue is what the kernel is made of
+constexpr int kC1Threads = (5 + kC1EpiWarps) * 32;
 constexpr int kC1Stages = 3;
 constexpr int kC1ATile = 128 * 128;             // 128 rows x 128-byte swizzle rows (K = 32 x f16 uses 64 B)
 constexpr int kC1EpiBuf = 32 * 64;              // 32 rows x 32 channels x 16 bit
 constexpr int kMelRowsC1 = 128;
 
 __host__ __device__ constexpr int c1_smem_bytes(int C) {
-    return C * 128 /*W image*/ + kC1Stages * kC1ATile + 8 * 2 * kC1EpiBuf + ((C * 4 + 255) / 256) * 256 /*bias*/ + 256 + 1024;
+    return C * 128 /*W image*/ + kC1Stages * kC1ATile + kC1EpiWarps * 2 * kC1EpiBuf + ((C * 4 + 255) / 256) * 256 /*bias*/ + 256 + 1024;
 }
 
 __device__ __forceinline__ float gelu_tanh6(float x) {
@@ -56,11 +57,11 @@ conv1_tc_kernel(const float* __restrict__ mel, const StemChunk* __restrict__ chu
     const uint32_t sW = base;
     const uint32_t sA = sW + C * 128;
     const uint32_t sE = sA + kC1Stages * kC1ATile;
-    const uint32_t sBias = sE + 8 * 2 * kC1EpiBuf;
+    const uint32_t sBias = sE + kC1EpiWarps * 2 * kC1EpiBuf;
     const uint32_t bars = sBias + ((C * 4 + 255) / 256) * 256;
     uint8_t* gA = gen + C * 128;
     uint8_t* gE = gA + kC1Stages * kC1ATile;
-    float* gBias = reinterpret_cast<float*>(gE + 8 * 2 * kC1EpiBuf);
+    float* gBias = reinterpret_cast<float*>(gE + kC1EpiWarps * 2 * kC1EpiBuf);
     auto a_full = [&](int s) { return bars + 8u * s; };
     auto a_empty = [&](int s) { return bars + 8u * (3 + s); };
     auto tfull = [&](int h) { return bars + 8u * (6 + h); };
@@ -79,7 +80,7 @@ conv1_tc_kernel(const float* __restrict__ mel, const StemChunk* __restrict__ chu
     if (tid == 0) {
         tc::prefetch_tmap(&tmap_out);
         for (int s = 0; s < kC1Stages; ++s) { tc::mbar_init(a_full(s), 4); tc::mbar_init(a_empty(s), 1); }
-        for (int h = 0; h < 2; ++h) { tc::mbar_init(tfull(h), 1); tc::mbar_init(tempty(h), 8); }
+        for (int h = 0; h < 2; ++h) { tc::mbar_init(tfull(h), 1); tc::mbar_init(tempty(h), kC1EpiWarps); }
         tc::fence_barrier_init();
     }
     if (warp == 4) tc::tmem_alloc<512>(tmem_slot);
@@ -189,7 +190,7 @@ conv1_tc_kernel(const float* __restrict__ mel, const StemChunk* __restrict__ chu
                 tc::fence_after_sync();
                 const uint32_t t_row = tmem + h * 256 + ((uint32_t)(q * 32) << 16);
 #pragma unroll 1
-                for (int c = hf; c < nch; c += 2) {
+                for (int c = hf; c < nch; c += kC1EpiWarps / 4) {
                     const int n0 = h * 256 + c * 32;
                     uint32_t pk[16];
                     if (valid) {

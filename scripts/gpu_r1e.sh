@@ -13,7 +13,9 @@ timeout 300 $CMD > gpurun_out/plain.log 2>&1 || exit 1
 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --print-units base --clock-control none \
   -s 405 -c 135 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 echo "ncu launches exit=$?"
-for spec in "mel_frames:prof_mel:3:1" "attention_kernel:prof_attn:60:1" "EpiBiasActOp.*1:prof_gemm_up:51:1" "LoaderConv.*Planes:prof_conv2:3:1" "conv1_tc:prof_conv1:3:1"; do
+# gemm_tc_kernel launches of a step, in order: conv2, conv3, conv_out, then per layer QKV, out, up, down (77 per step);
+# after 3 warm-up steps: conv2 = #231, layer-0 up-projection = #236, layer-0 down-projection = #237
+for spec in "mel_frames:prof_mel:3:1" "attention_kernel:prof_attn:60:1" "gemm_tc_kernel:prof_conv2:231:1" "gemm_tc_kernel:prof_gemm_up:236:2" "conv1_tc:prof_conv1:3:1"; do
   IFS=: read pat name skip cnt <<< "$spec"
   timeout 600 ncu --set full --clock-control none --import-source on -k "regex:$pat" -s $skip -c $cnt -f -o gpurun_out/$name $CMD > gpurun_out/ncu_$name.log 2>&1
   echo "ncu $name exit=$?"

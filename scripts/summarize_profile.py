@@ -98,7 +98,7 @@ def launches(tag: str) -> None:
 def full_reports(tag: str) -> None:
     out_rows = []
     for rep in sorted(glob.glob(os.path.join(GO, "prof_*.ncu-rep"))):
-        r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True)
+        r = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--print-units", "base"], capture_output=True, text=True)
         if r.returncode != 0:
             print("ncu -i failed on", rep, r.stderr[:200])
             continue
