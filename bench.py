@@ -287,14 +287,19 @@ def run_ours(args):
     gemm_tf = g_fl / g_ms / 1e9
     mel_bytes = BATCH * (4 * n + 4 * 128 * (n // 160)) * args.steps
     mel_gbs = mel_bytes / (mel_ms / 1e3) / 1e9
-    traffic = None
+    # DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum), from the committed launch list of this
+    # same workload (profiles/roofline_traffic.json, written by scripts/summarize_profile.py); null without it
+    traffic = traffic_attn = traffic_mel = None
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
         try:
             with open(tp) as f:
-                traffic = json.load(f).get("gemm_tc_kernel_dram_bytes_per_launch")
+                tj = json.load(f)
+            traffic = tj.get("gemm_tc_kernel_dram_bytes_per_launch")
+            traffic_attn = tj.get("attention_kernel_dram_bytes_per_launch")
+            traffic_mel = tj.get("mel_frames_kernel_dram_bytes_per_launch")
         except Exception:
-            traffic = None
+            pass
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -322,9 +327,10 @@ def run_ours(args):
                      "how": "algorithmic FLOPs (2*M*N*K, no padding) / CUDA-event time of every launch, separate profiled pass of the same K steps"},
         "roofline_attention": {"bound": "tensor", "kernel": "attention_kernel (tcgen05 varlen attention)",
                                "achieved": a_fl / a_ms / 1e9, "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
-                               "frac": a_fl / a_ms / 1e9 / pk["tflops_sustained"], "ms_per_step": a_ms / args.steps},
+                               "frac": a_fl / a_ms / 1e9 / pk["tflops_sustained"], "ms_per_step": a_ms / args.steps,
+                               "traffic": traffic_attn},
         "roofline_mel": {"bound": "hbm", "kernel": "mel_frames_kernel (+ max decode)", "achieved": mel_gbs, "peak": pk["hbm_gbs"],
-                         "unit": "GB/s", "frac": mel_gbs / pk["hbm_gbs"], "ms_per_step": mel_ms / args.steps,
+                         "unit": "GB/s", "frac": mel_gbs / pk["hbm_gbs"], "ms_per_step": mel_ms / args.steps, "traffic": traffic_mel,
                          "how": "(4*n_samples + 4*128*n_len) per clip / CUDA-event time"},
         "stage_ms_per_step": {"mel_spectrogram": mel_ms / args.steps, "audio_encoding.conv_chunk": stem_ms / args.steps,
                               "audio_encoding.transformer": x_ms / args.steps},

@@ -171,6 +171,14 @@ int64_t q3a_encoder_device_bytes(const q3a_encoder* enc);
  * a*T + b*sum(seg^2); shard_of[i] receives the shard of utterance i.  Deterministic. Host only. */
 int q3a_plan_shards(const int* n_frames, int n_utts, int mode, int n_shards, int* shard_of);
 
+/* How a q3a_encode_pcm_batch call over these clips is scheduled: pass_of[i] (a pass bounds the stem workspace;
+ * consecutive passes overlap as upload | compute | download), in_part_of[i] (upload part inside the pass: the stem of a
+ * part starts as soon as its PCM has landed) and out_part_of[i] (download part: its rows travel back while the next
+ * part runs its last layers).  out_width = 1024 (or d_model for Q3A_MODE_CONV_ONLY).  Host only; results never
+ * depend on the schedule. */
+int q3a_plan_host_call(const int* n_samples, int n_clips, int mode, int out_width, int* pass_of, int* in_part_of,
+                       int* out_part_of);
+
 /* ---- unit-test hooks for the tensor-core building blocks (device pointers) ---------------- */
 
 /* D[M][N] (f32) = A[M][K] * W[N][K]^T (+bias[N]) ; A, W are 16-bit (operand_dtype) row-major.

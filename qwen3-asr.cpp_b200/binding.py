@@ -64,6 +64,7 @@ SYMBOLS = {
     "q3a_encoder_get_timings": (_I, [_P, C.POINTER(Timings)]),
     "q3a_encoder_device_bytes": (_I64, [_P]),
     "q3a_plan_shards": (_I, [_P, _I, _I, _I, _P]),
+    "q3a_plan_host_call": (_I, [_P, _I, _I, _I, _P, _P, _P]),
     "q3a_test_gemm": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "q3a_test_attention": (_I, [_P, _P, _I, _I, _P, _I, _I, _P]),
 }
@@ -242,6 +243,14 @@ class Encoder:
 
     def device_bytes(self) -> int:
         return int(self.lib.q3a_encoder_device_bytes(self.h))
+
+
+def plan_host_call(n_samples, mode: int, out_width: int = 1024) -> tuple[list[int], list[int], list[int]]:
+    """(pass, upload part, download part) of every clip of a q3a_encode_pcm_batch call"""
+    n = len(n_samples)
+    a, b, c = (C.c_int * max(n, 1))(), (C.c_int * max(n, 1))(), (C.c_int * max(n, 1))()
+    check(load().q3a_plan_host_call(_int_array(n_samples), n, mode, out_width, a, b, c))
+    return list(a)[:n], list(b)[:n], list(c)[:n]
 
 
 def plan_shards(n_frames, mode: int, n_shards: int) -> list[int]:

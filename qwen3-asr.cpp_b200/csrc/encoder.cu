@@ -723,6 +723,39 @@ static const double kOne[1] = {1.0};
 // output part travel back while the second runs its last layers.
 constexpr long long kSplitMinBytes = 16ll << 20;
 
+// Host-side plan of one host-pointer call: passes, staging offsets, upload / download parts of every pass.
+struct HostPlan {
+    std::vector<int> bounds;                       // pass p = utterances [bounds[p], bounds[p+1])
+    std::vector<std::vector<int64_t>> ioff;        // per pass: element offset of every utterance in the staging buffer
+    std::vector<std::vector<int>> in_split, out_split;   // per pass: part boundaries (pass-relative utterance indices)
+    std::vector<long long> tokens;                 // per pass: output rows
+};
+
+static void plan_host_call(const int* in_elems, int elem_bytes, int64_t align_elems, const int* n_frames, int n, int mode,
+                           int width, bool split_ok, HostPlan& plan) {
+    plan_passes(n_frames, n, mode, plan.bounds);
+    const int n_pass = (int)plan.bounds.size() - 1;
+    plan.ioff.assign(n_pass, {}); plan.in_split.assign(n_pass, {}); plan.out_split.assign(n_pass, {});
+    plan.tokens.assign(n_pass, 0);
+    for (int p = 0; p < n_pass; ++p) {
+        const int u0 = plan.bounds[p], nu = plan.bounds[p + 1] - u0;
+        q3a_pack_offsets(in_elems + u0, nu, 1, align_elems, plan.ioff[p]);
+        std::vector<long long> w_in(nu), w_out(nu);
+        long long T = 0;
+        for (int i = 0; i < nu; ++i) {
+            w_in[i] = in_elems[u0 + i];
+            w_out[i] = encoder_n_tokens(n_frames[u0 + i], mode);
+            T += w_out[i];
+        }
+        plan.tokens[p] = T;
+        const long long in_bytes = (long long)elem_bytes * plan.ioff[p][nu], out_bytes = 4ll * T * width;
+        plan.in_split[p] = split_ok && in_bytes >= kSplitMinBytes ? weighted_split(w_in, q3a_encoder::kInParts, kInFrac)
+                                                                  : weighted_split(w_in, 1, kOne);
+        plan.out_split[p] = split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY
+                                ? weighted_split(w_out, q3a_encoder::kOutParts, kOutFrac) : weighted_split(w_out, 1, kOne);
+    }
+}
+
 template <class Compute>
 static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_elems, int elem_bytes, int64_t align_elems,
                            const int* n_frames, int n, int mode, int width, float* const* out, int* n_tokens, Compute compute) {
@@ -732,32 +765,19 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
         if (trace) fprintf(stderr, "[q3a trace] %-28s %8.3f ms\n", what,
                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
     };
-    std::vector<int> bounds;
-    plan_passes(n_frames, n, mode, bounds);
+    HostPlan plan;
+    plan_host_call(in_elems, elem_bytes, align_elems, n_frames, n, mode, width, getenv("Q3A_NO_PART_OVERLAP") == nullptr, plan);
+    const std::vector<int>& bounds = plan.bounds;
+    const std::vector<std::vector<int64_t>>& ioff = plan.ioff;
+    const std::vector<std::vector<int>>&in_split = plan.in_split, &out_split = plan.out_split;
     const int n_pass = (int)bounds.size() - 1;
     DevBuf* sin[2] = {&e->stage_in, &e->stage_in2};
     DevBuf* sout[2] = {&e->stage_out, &e->stage_out2};
-    // offsets, partition and buffer sizes of every pass, reserved up front (nothing is in flight yet)
-    std::vector<std::vector<int64_t>> ioff(n_pass);
-    std::vector<std::vector<int>> in_split(n_pass), out_split(n_pass);
     size_t need_in[2] = {0, 0}, need_out[2] = {0, 0};
-    const bool split_ok = getenv("Q3A_NO_PART_OVERLAP") == nullptr;
     for (int p = 0; p < n_pass; ++p) {
-        const int u0 = bounds[p], nu = bounds[p + 1] - u0;
-        q3a_pack_offsets(in_elems + u0, nu, 1, align_elems, ioff[p]);
-        std::vector<long long> w_in(nu), w_out(nu);
-        long long T = 0;
-        for (int i = 0; i < nu; ++i) {
-            w_in[i] = in_elems[u0 + i];
-            w_out[i] = encoder_n_tokens(n_frames[u0 + i], mode);
-            T += w_out[i];
-        }
-        const long long in_bytes = (long long)elem_bytes * ioff[p][nu], out_bytes = 4ll * T * width;
-        in_split[p] = split_ok && in_bytes >= kSplitMinBytes ? weighted_split(w_in, q3a_encoder::kInParts, kInFrac) : weighted_split(w_in, 1, kOne);
-        out_split[p] = split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY ? weighted_split(w_out, q3a_encoder::kOutParts, kOutFrac)
-                                                                                               : weighted_split(w_out, 1, kOne);
+        const int nu = bounds[p + 1] - bounds[p];
         need_in[p & 1] = std::max(need_in[p & 1], (size_t)elem_bytes * (size_t)(ioff[p][nu] + align_elems));
-        need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)T * width + 64));
+        need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)plan.tokens[p] * width + 64));
     }
     for (int b = 0; b < 2; ++b) {
         if (need_in[b]) Q3A_TRY(sin[b]->reserve(need_in[b]));
@@ -977,6 +997,32 @@ extern "C" int q3a_encode_pcm16_batch(q3a_frontend* fe, q3a_encoder* e, const in
                                 return pcm_core(fe, e, mono, foff.data(), n_samples + u0, nu, mode, out_dev, nullptr, e->stream, &mine);
                             }));
     return prof_collect(e, e->stream);
+}
+
+// Test / inspection hook for the planner above: which pass, upload part and download part every utterance of a
+// q3a_encode_pcm_batch call lands in.  Host only.
+extern "C" int q3a_plan_host_call(const int* n_samples, int n_clips, int mode, int out_width, int* pass_of, int* in_part_of,
+                                  int* out_part_of) {
+    if (n_clips < 0 || (n_clips > 0 && (!n_samples || !pass_of || !in_part_of || !out_part_of)) || out_width <= 0) {
+        set_error("plan_host_call: bad argument"); return Q3A_ERR_ARG;
+    }
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("plan_host_call: unknown mode"); return Q3A_ERR_ARG; }
+    std::vector<int> nf(n_clips);
+    for (int i = 0; i < n_clips; ++i) {
+        if (n_samples[i] < 0) { set_error("plan_host_call: negative n_samples"); return Q3A_ERR_ARG; }
+        nf[i] = n_samples[i] / 160;
+    }
+    HostPlan plan;
+    plan_host_call(n_samples, 4, 64, nf.data(), n_clips, mode, out_width, true, plan);
+    for (size_t p = 0; p + 1 < plan.bounds.size(); ++p) {
+        const int u0 = plan.bounds[p];
+        for (int i = u0; i < plan.bounds[p + 1]; ++i) pass_of[i] = (int)p;
+        for (size_t k = 0; k + 1 < plan.in_split[p].size(); ++k)
+            for (int i = plan.in_split[p][k]; i < plan.in_split[p][k + 1]; ++i) in_part_of[u0 + i] = (int)k;
+        for (size_t k = 0; k + 1 < plan.out_split[p].size(); ++k)
+            for (int i = plan.out_split[p][k]; i < plan.out_split[p][k + 1]; ++i) out_part_of[u0 + i] = (int)k;
+    }
+    return Q3A_OK;
 }
 
 // Longest-processing-time-first assignment.  Cost model: per token ~0.71 GFLOP of dense work plus the

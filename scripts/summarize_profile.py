@@ -90,8 +90,13 @@ def launches(tag: str) -> None:
     g = traffic.get("gemm_tc_kernel")
     if g and g["launches"] and g["dram_bytes"] > 0:
         with open(os.path.join(PROF, "roofline_traffic.json"), "w") as f:       # read by bench.py -> roofline.traffic
-            json.dump({"gemm_tc_kernel_dram_bytes_per_launch": g["dram_bytes"] / g["launches"], "launches_per_step": g["launches"],
-                       "source": f"profiles/{tag}_traffic.json"}, f, indent=1)
+            out = {"gemm_tc_kernel_dram_bytes_per_launch": g["dram_bytes"] / g["launches"], "launches_per_step": g["launches"],
+                   "source": f"profiles/{tag}_traffic.json"}
+            for fam in ("attention_kernel", "mel_frames_kernel"):
+                t = traffic.get(fam)
+                if t and t["launches"]:
+                    out[f"{fam}_dram_bytes_per_launch"] = t["dram_bytes"] / t["launches"]
+            json.dump(out, f, indent=1)
     print("wrote", f"profiles/{tag}_launches.md", f"profiles/{tag}_traffic.json")
 
 

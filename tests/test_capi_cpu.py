@@ -87,3 +87,35 @@ def test_compute_fails_loudly_without_gpu(lib, tiny_models):
     h = C.c_void_p()
     assert lib.q3a_encoder_load(models["f16"][0].encode(), 0, B.OP_BF16, C.byref(h)) == 2
     assert not h.value
+
+
+def test_host_call_schedule(lib):
+    """The host-pointer entry points cut a call into passes and, inside a pass, into upload / download parts so that
+    PCIe copies hide under kernels.  Pure host logic: contiguous, monotone, bounded, and small calls stay whole."""
+    n30 = 480000
+    # BASELINE config 2: one pass, 4 upload parts (the first one small: only its copy is exposed), 2 download halves
+    ps, ip, op = B.plan_host_call([n30] * 64, B.MODE_ASR)
+    assert set(ps) == {0}
+    assert ip == sorted(ip) and sorted(set(ip)) == [0, 1, 2, 3]
+    assert 4 <= ip.count(0) <= 8 and all(16 <= ip.count(k) <= 22 for k in (1, 2, 3))
+    assert op == sorted(op) and op.count(0) == 32 and op.count(1) == 32
+    # a small call is not partitioned at all
+    ps, ip, op = B.plan_host_call([n30] * 3, B.MODE_ASR)
+    assert set(ps) == set(ip) == set(op) == {0}
+    # conv-only output is never split (no transformer tail to hide a download under)
+    assert set(B.plan_host_call([n30] * 64, B.MODE_CONV_ONLY, 896)[2]) == {0}
+    # a 10-h ragged corpus: passes bounded by 4096 stem chunks, everything contiguous and monotone
+    rng = np.random.default_rng(500)
+    lens = [int(16000 * np.exp(rng.uniform(np.log(2), np.log(60)))) for _ in range(1700)]
+    ps, ip, op = B.plan_host_call(lens, B.MODE_ASR)
+    assert ps == sorted(ps) and ps[0] == 0 and len(set(ps)) >= 2
+    for p in set(ps):
+        idx = [i for i, q in enumerate(ps) if q == p]
+        assert idx == list(range(idx[0], idx[-1] + 1))
+        assert sum(-(-(lens[i] // 160) // 100) for i in idx) <= 4096
+        sub_in, sub_out = [ip[i] for i in idx], [op[i] for i in idx]
+        assert sub_in == sorted(sub_in) and sub_in[0] == 0 and max(sub_in) <= 3
+        assert sub_out == sorted(sub_out) and sub_out[0] == 0 and max(sub_out) <= 1
+    assert B.plan_host_call([], B.MODE_ASR) == ([], [], [])
+    with pytest.raises(B.Q3AError):
+        B.plan_host_call([-1], B.MODE_ASR)

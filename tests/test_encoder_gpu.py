@@ -136,6 +136,29 @@ def test_asr_06b_q8_file(lib, asr_model, filters):
     enc.close()
 
 
+def test_asr_06b_92s_clip_full_attention(lib, asr_model, filters):
+    """BASELINE config 3's length: one 92-s clip = 1196 tokens attended as ONE sequence, the way the reference runs
+    it (audio_encoder.cpp:466-486 has no mask): ten query tiles, nineteen key blocks with the lazily rescaled running
+    maximum; and the same audio cut into 30 + 30 + 30 + 2 s utterances (the north star's "chunked" reading), each equal
+    to that piece encoded on its own."""
+    shape, paths, Ws = asr_model
+    enc = B.Encoder(paths["f16"], 0, B.OP_BF16)
+    fe = B.Frontend(0)
+    pcm = synth.synth_audio(301, 16000 * 92)
+    mel = MO.log_mel_numpy(pcm, filters)
+    got = enc.encode_batch([mel], B.MODE_ASR)[0]
+    want = _oracle(mel, Ws["f16"], shape, "asr")
+    assert got.shape == want.shape == (1196, 1024)
+    cos, rel = compare(got, want)
+    assert cos >= COS and rel <= REL, (cos, rel)
+    pieces = [pcm[:480000], pcm[480000:960000], pcm[960000:1440000], pcm[1440000:]]
+    outs = enc.encode_pcm_batch(fe, pieces, B.MODE_ASR)
+    assert [o.shape[0] for o in outs] == [390, 390, 390, 26]
+    for piece, o in zip(pieces, outs):
+        assert np.array_equal(o, enc.encode_pcm_batch(fe, [piece], B.MODE_ASR)[0])
+    enc.close(); fe.close()
+
+
 def test_pcm_path_batch_invariance_and_full_size(lib, asr_model, filters):
     """BASELINE config 2 shape (64 x 30 s, bf16): the fused PCM->features call; a clip's features do not depend on
     what else is in the batch (bit-identical), and agree with the oracle on a spot-checked clip."""
