@@ -1,0 +1,60 @@
+"""Throughput of BASELINE.json configs 3, 4 and 5 on one B200 through the host-pointer C ABI (q3a_encode_pcm_batch:
+pinned host PCM in, pinned host features out).  Config 2 is bench.py's line; these are parity-test cases whose speed is
+recorded for DESIGN.md.  Writes gpurun_out/configs.json."""
+import json, os, sys, tempfile, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import ctypes as C
+import numpy as np, torch
+import q3a_b200  # noqa
+from q3a_b200 import binding as B, synth
+
+B.load()
+tmp = tempfile.mkdtemp()
+res = {}
+
+
+def run(name, enc, fe, lens, mode, reps=4):
+    base = synth.synth_audio(77, max(lens))
+    hosts = [torch.from_numpy(np.ascontiguousarray(base[:n])).pin_memory() for n in lens]
+    outs = [torch.empty((max(enc.n_tokens(n // 160, mode), 1), enc.hp.out_dim), dtype=torch.float32).pin_memory() for n in lens]
+    k = len(lens)
+    pp = (C.c_void_p * k)(*[h.data_ptr() for h in hosts]); po = (C.c_void_p * k)(*[o.data_ptr() for o in outs])
+    ns = (C.c_int * k)(*lens); nt = (C.c_int * k)()
+    def call():
+        B.check(enc.lib.q3a_encode_pcm_batch(fe.h, enc.h, pp, ns, k, mode, po, nt))
+    call(); call()
+    ts = []
+    for _ in range(reps):
+        t0 = time.perf_counter(); call(); ts.append(time.perf_counter() - t0)
+    secs = sum(lens) / 16000.0
+    best, med = min(ts), sorted(ts)[len(ts) // 2]
+    res[name] = {"utterances": k, "audio_s": secs, "tokens": int(sum(nt)), "ms_median": med * 1e3, "ms_best": best * 1e3,
+                 "audio_s_per_s_median": secs / med, "device_bytes": enc.device_bytes()}
+    print(name, json.dumps(res[name]), flush=True)
+
+
+fe = B.Frontend(0)
+# config 3: ASR-0.6B, Q8_0 GGUF, 8 x 92-s clips: (a) one 1196-token full-attention sequence per clip, (b) cut into 30-s pieces
+shape = synth.ASR_06B
+w = synth.random_weights(shape, 0)
+enc = B.Encoder(synth.write_gguf(os.path.join(tmp, "asr_q8.gguf"), shape, w, "q8_0"), 0, B.OP_BF16)
+run("config3_q8_92s_full_attention", enc, fe, [92 * 16000] * 8, B.MODE_ASR)
+run("config3_q8_92s_cut_30s", enc, fe, [480000, 480000, 480000, 32000] * 8, B.MODE_ASR)
+enc.close()
+# config 5 (per-GPU share of the 10-h corpus at 8 GPUs = 4500 s): log-uniform 2-60 s utterances, ASR bf16
+enc = B.Encoder(synth.write_gguf(os.path.join(tmp, "asr_f16.gguf"), shape, w, "f16"), 0, B.OP_BF16)
+rng = np.random.default_rng(500)
+lens, tot = [], 0.0
+while tot < 4500.0:
+    s = float(np.exp(rng.uniform(np.log(2), np.log(60)))); lens.append(int(s * 16000)); tot += s
+run("config5_ragged_4500s_shard", enc, fe, lens, B.MODE_ASR)
+enc.close(); del w
+# config 4: aligner-0.6B (24 layers, d 1024), 64 utterances U[5,120] s, padded-tail stem, 104-token windows
+shape = synth.ALIGNER_06B
+w = synth.random_weights(shape, 1)
+enc = B.Encoder(synth.write_gguf(os.path.join(tmp, "al_f16.gguf"), shape, w, "f16"), 0, B.OP_BF16)
+rng = np.random.default_rng(400)
+run("config4_aligner_64x5-120s", enc, fe, [int(rng.uniform(5, 120) * 16000) for _ in range(64)], B.MODE_ALIGNER)
+enc.close()
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(res, open("gpurun_out/configs.json", "w"), indent=1)
