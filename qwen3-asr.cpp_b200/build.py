@@ -20,7 +20,7 @@ OBJ = os.path.join(HERE, "build")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC,-O3", "--expt-relaxed-constexpr", "-Xptxas", "-v",
-         "-DQ3A_BUILD"] + (["-DQ3A_ATTN_TIMELINE"] if os.environ.get("Q3A_ATTN_TIMELINE") else [])
+         "-DQ3A_BUILD"]
 
 
 def sources() -> list[str]:
