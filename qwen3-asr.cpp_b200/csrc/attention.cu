@@ -352,10 +352,12 @@ static int attention_launch_kt(const void* qkv, void* out, int T, int d, const A
     Q3A_TRY(make_tmap_2d(&tm_q, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, 128));
     Q3A_TRY(make_tmap_2d(&tm_kv, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, KT));
     auto kern = attention_kernel<OpT, KT>;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[64] = {false};              // the opt-in is per device
+    int dev = 0;
+    Q3A_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
         Q3A_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem));
-        attr_set = true;
+        if (dev >= 0 && dev < 64) attr_set[dev] = true;
     }
     Q3A_CUDA(launch_pdl(kern, dim3(n_tiles, n_heads), dim3(128), Cfg::kSmem, stream, tm_q, tm_kv, tiles_dev, (OpT*)out, d));
     ++g_launch_counter;
