@@ -93,3 +93,40 @@ def test_variants_differ_only_where_the_reference_differs():
     a = EO.stem_asr(ragged, W, shape.d_model, nm)
     b = EO.stem_aligner(ragged, W, shape.d_model, nm)
     assert a.shape == b.shape and np.array_equal(a[:26], b[:26]) and not np.array_equal(a[26:], b[26:])
+
+
+HF_GOLD = os.path.join(os.path.dirname(__file__), "golden", "hf_audio_tower_tiny.npz")
+
+
+def test_graph_matches_upstream_hf_audio_tower():
+    """tests/golden/hf_audio_tower_tiny.npz holds outputs of transformers' Qwen3OmniMoeAudioEncoder -- the class whose
+    parameters the reference's converter maps onto the GGUF tensors (convert_hf_to_gguf.py:48-103) -- on the tiny tower
+    in float64 (make_hf_golden.py).  The restatement in its ideal mode, with the exact erf GELU the HF code uses, must
+    reproduce them: this pins weight layouts, feature order, chunk padding, per-chunk positions, windows and layer
+    order to an implementation that is not ours.  ggml's tanh-form GELU then moves the result by ~3e-4."""
+    g = np.load(HF_GOLD)
+    shape = synth.tiny_shape()
+    w = synth.random_weights(shape, 7)
+    W = EO.Weights({k: v for k, v in synth.stored_weights(w, "f32").items() if "#" not in k}, "f32")
+    filt = np.load(os.path.join(os.path.dirname(GOLD), "mel_ref.npz"))["filters"]
+    erf = EO.Numerics(act_round="none", gelu_table=False, gelu_erf=True, dtype=np.float64)
+    for key in [k for k in g.files if k.startswith("win_")]:
+        _, seed, n = key.split("_")
+        mel = MO.log_mel_numpy(synth.synth_audio(int(seed), int(n)), filt)
+        kw = dict(n_layers=shape.n_layers, d_model=shape.d_model, n_heads=shape.n_heads)
+        # flash-attention reading: 104-token windows = ForcedAligner::encode_audio
+        win = EO.encode(mel, W, variant="aligner", nm=erf, **kw)
+        assert win.shape == g[key].shape
+        assert np.abs(win - g[key]).max() <= 2e-6 * np.abs(g[key]).max()
+        assert [int(c) for c in g[f"cu_{seed}_{n}"]] == [0] + [b for _, b in EO.window_segments(win.shape[0], 104)]
+        # eager reading: padded stem, every token attends to every token
+        h = EO.stem_aligner(mel, W, shape.d_model, erf)
+        full = EO.transformer(h, W, shape.n_layers, shape.n_heads, 1e-5, EO.window_segments(h.shape[0], 0), erf)
+        want = g[f"full_{seed}_{n}"]
+        assert np.abs(full - want).max() <= 2e-6 * np.abs(want).max()
+        if mel.shape[1] % 100 == 0:                      # no ragged tail: AudioEncoder::encode is that same graph
+            asr = EO.encode(mel, W, variant="asr", nm=erf, **kw)
+            assert np.abs(asr - want).max() <= 2e-6 * np.abs(want).max()
+        # the price of ggml's tanh-form GELU (audio_encoder.cpp:112 -> ggml_gelu) against the upstream erf form
+        tanh = EO.encode(mel, W, variant="aligner", nm=EO.IDEAL, **kw)
+        assert np.abs(tanh - g[key]).max() <= 1e-3 * np.abs(g[key]).max()
