@@ -190,6 +190,16 @@ int q3a_test_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, f
 int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
                        int operand_dtype, void* stream);
 
+/* The library's own bounds check (compute-sanitizer's stand-in where that tool is not available).  With Q3A_GUARD=1
+ * in the environment when the process first allocates, every device buffer the library owns (weights, activations,
+ * staging, descriptor tables) is exact-size and fenced by two 4-KiB pattern bands.  This call synchronises the
+ * current device, reads every live band back and reports how many exist and how many were written to;
+ * q3a_last_error() then names the damaged buffers.  Q3A_ERR_STATE if the mode is off. */
+int q3a_debug_check_guards(int* n_bands, int* n_damaged);
+/* Self-test of the detector: writes one byte just past the end of one live guarded buffer, so that the next
+ * q3a_debug_check_guards reports exactly one damaged band. */
+int q3a_debug_damage_guard(void);
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,8 @@ SYMBOLS = {
     "q3a_plan_host_call": (_I, [_P, _I, _I, _I, _P, _P, _P]),
     "q3a_test_gemm": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "q3a_test_attention": (_I, [_P, _P, _I, _I, _P, _I, _I, _P]),
+    "q3a_debug_check_guards": (_I, [_P, _P]),
+    "q3a_debug_damage_guard": (_I, []),
 }
 
 _lib = None
@@ -272,3 +274,11 @@ def test_attention(qkv, out, n_heads: int, cu_seqlens, operand: int) -> None:
     cu = _int_array(cu_seqlens)
     check(load().q3a_test_attention(qkv.data_ptr(), out.data_ptr(), T, n_heads, cu, len(cu_seqlens) - 1, operand,
                                     None))
+
+
+def check_guards() -> tuple[int, int]:
+    """(bands, damaged) over every live device buffer of the library; needs Q3A_GUARD=1 in the environment before the
+    first allocation (include/q3a.h: q3a_debug_check_guards)."""
+    n, bad = C.c_int(0), C.c_int(0)
+    check(load().q3a_debug_check_guards(C.byref(n), C.byref(bad)))
+    return n.value, bad.value

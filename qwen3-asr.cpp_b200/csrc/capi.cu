@@ -2,7 +2,10 @@
 // selection (sm_100 only - there is no other code path), version.
 #include "common.cuh"
 
+#include <cstdlib>
+#include <map>
 #include <mutex>
+#include <vector>
 
 namespace q3a {
 
@@ -33,7 +36,63 @@ int use_device(int device) {
     return Q3A_OK;
 }
 
+// ---- Q3A_GUARD: guard bands around every DevBuf allocation (see common.cuh) ------------------------------
+static std::mutex g_guard_mu;
+static std::map<void*, size_t> g_guards;            // cudaMalloc base -> user bytes between the bands
+
+bool guard_enabled() {
+    static const bool on = [] { const char* e = getenv("Q3A_GUARD"); return e && *e && *e != '0'; }();
+    return on;
+}
+void guard_register(void* base, size_t user_bytes) {
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    g_guards[base] = user_bytes;
+}
+void guard_forget(void* base) {
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    g_guards.erase(base);
+}
+
 }  // namespace q3a
+
+// Every live guarded allocation of the process: both bands copied back and compared with the fill pattern.
+extern "C" int q3a_debug_check_guards(int* n_bands, int* n_damaged) {
+    using namespace q3a;
+    if (!n_bands || !n_damaged) { set_error("debug_check_guards: null argument"); return Q3A_ERR_ARG; }
+    *n_bands = *n_damaged = 0;
+    if (!guard_enabled()) { set_error("debug_check_guards: Q3A_GUARD was not set when the library allocated"); return Q3A_ERR_STATE; }
+    Q3A_CUDA(cudaDeviceSynchronize());
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    std::vector<unsigned char> host(kGuardBytes);
+    std::string where;
+    for (const auto& kv : g_guards) {
+        for (int side = 0; side < 2; ++side) {
+            const char* band = static_cast<const char*>(kv.first) + (side ? kGuardBytes + kv.second : 0);
+            Q3A_CUDA(cudaMemcpy(host.data(), band, kGuardBytes, cudaMemcpyDefault));
+            ++*n_bands;
+            size_t bad = 0, first = 0;
+            for (size_t i = 0; i < kGuardBytes; ++i)
+                if (host[i] != 0xA5) { if (!bad) first = i; ++bad; }
+            if (bad) {
+                ++*n_damaged;
+                where += (side ? " after" : " before") + std::string(" a ") + std::to_string(kv.second) + "-byte buffer (" +
+                         std::to_string(bad) + " bytes, first at band offset " + std::to_string(first) + ");";
+            }
+        }
+    }
+    if (*n_damaged) set_error("guard bands damaged:" + where);
+    return Q3A_OK;
+}
+
+// Detector self-test: one byte written just past the end of the first live guarded buffer.
+extern "C" int q3a_debug_damage_guard(void) {
+    using namespace q3a;
+    std::lock_guard<std::mutex> lk(g_guard_mu);
+    if (g_guards.empty()) { set_error("debug_damage_guard: no guarded buffer is live"); return Q3A_ERR_STATE; }
+    const auto& kv = *g_guards.begin();
+    Q3A_CUDA(cudaMemset(static_cast<char*>(kv.first) + kGuardBytes + kv.second, 0, 1));
+    return Q3A_OK;
+}
 
 extern "C" const char* q3a_last_error(void) { return q3a::last_error(); }
 extern "C" int q3a_version(void) { return 100; }

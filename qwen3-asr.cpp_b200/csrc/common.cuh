@@ -80,18 +80,44 @@ __host__ __device__ constexpr int64_t round_up64(int64_t a, int64_t b) { return 
 
 // ---- small RAII helpers (host) ---------------------------------------------------------------
 // Growable device buffer: keeps its allocation between calls, grows geometrically.
+// With Q3A_GUARD set in the environment every allocation is exact-size and sits between two 4-KiB bands of a
+// known byte pattern, registered with guard_check(): the library's own bounds check (q3a_debug_check_guards),
+// since an out-of-range store by any kernel lands in a band instead of in the growth slack.
+constexpr size_t kGuardBytes = 4096;
+bool guard_enabled();
+void guard_register(void* base, size_t user_bytes);
+void guard_forget(void* base);
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
+    void* base = nullptr;            // what cudaMalloc returned (== p unless guarded)
     int reserve(size_t bytes) {
         if (bytes <= cap) return Q3A_OK;
-        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        release();
+        if (guard_enabled()) {
+            const size_t user = (bytes + 255) & ~size_t(255);
+            Q3A_CUDA(cudaMalloc(&base, user + 2 * kGuardBytes));
+            Q3A_CUDA(cudaMemset(base, 0xA5, kGuardBytes));
+            Q3A_CUDA(cudaMemset(static_cast<char*>(base) + kGuardBytes + user, 0xA5, kGuardBytes));
+            p = static_cast<char*>(base) + kGuardBytes;
+            cap = user;
+            guard_register(base, user);
+            return Q3A_OK;
+        }
         size_t want = bytes + bytes / 8 + 256;
-        Q3A_CUDA(cudaMalloc(&p, want));
+        Q3A_CUDA(cudaMalloc(&base, want));
+        p = base;
         cap = want;
         return Q3A_OK;
     }
-    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    void release() {
+        if (base) {
+            if (p != base) guard_forget(base);
+            cudaFree(base);
+        }
+        p = base = nullptr;
+        cap = 0;
+    }
     template <class T> T* as() const { return reinterpret_cast<T*>(p); }
 };
 

@@ -714,8 +714,28 @@ static std::vector<int> weighted_split(const std::vector<long long>& weight, int
 }
 // uploads: a small first part (only its copy is exposed), then equal parts; downloads: halves
 static const double kInFrac[4] = {0.10, 0.40, 0.70, 1.0};
-static const double kOutFrac[2] = {0.5, 1.0};
 static const double kOne[1] = {1.0};
+// Download split and the number of trailing layers run per download part.  Tuning switches (not API):
+// Q3A_OUT_FRAC="0.4,0.75,1" (ascending cumulative fractions, at most kOutParts), Q3A_TAIL_LAYERS=n.
+struct OutSplit { double frac[q3a_encoder::kOutParts]; int parts; int tail_layers; };
+static OutSplit out_split_config() {
+    OutSplit c{{0.5, 1.0, 1.0, 1.0}, 2, 3};
+    if (const char* f = getenv("Q3A_OUT_FRAC")) {
+        int n = 0;
+        double prev = 0.0;
+        for (const char* p = f; *p && n < q3a_encoder::kOutParts;) {
+            char* end = nullptr;
+            const double v = strtod(p, &end);
+            if (end == p) break;
+            if (v > prev && v <= 1.0) { c.frac[n++] = v; prev = v; }
+            p = *end == ',' ? end + 1 : end;
+            if (*end != ',') break;
+        }
+        if (n > 0) { c.frac[n - 1] = 1.0; c.parts = n; }
+    }
+    if (const char* t = getenv("Q3A_TAIL_LAYERS")) c.tail_layers = std::max(0, atoi(t));
+    return c;
+}
 
 // The pipeline itself.  `in[i]` has `in_elems[i]` floats on the host; `compute(u0, nu, in_dev, in_off, out_dev,
 // hooks)` enqueues the pass on e->stream.  Inside a pass the upload is cut into kInParts and the download into
@@ -751,8 +771,9 @@ static void plan_host_call(const int* in_elems, int elem_bytes, int64_t align_el
         const long long in_bytes = (long long)elem_bytes * plan.ioff[p][nu], out_bytes = 4ll * T * width;
         plan.in_split[p] = split_ok && in_bytes >= kSplitMinBytes ? weighted_split(w_in, q3a_encoder::kInParts, kInFrac)
                                                                   : weighted_split(w_in, 1, kOne);
+        const OutSplit oc = out_split_config();
         plan.out_split[p] = split_ok && out_bytes >= kSplitMinBytes && mode != Q3A_MODE_CONV_ONLY
-                                ? weighted_split(w_out, q3a_encoder::kOutParts, kOutFrac) : weighted_split(w_out, 1, kOne);
+                                ? weighted_split(w_out, oc.parts, oc.frac) : weighted_split(w_out, 1, kOne);
     }
 }
 
@@ -812,6 +833,7 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
         PartHooks hk;
         hk.in_split = in_split[p];
         hk.out_split = out_split[p];
+        hk.tail_layers = out_split_config().tail_layers;
         hk.before_stem = [&, b](int part, int, int) -> int {
             if (part == 0) stamp("first before_stem");
             HOOK_CUDA(cudaStreamWaitEvent(e->stream, e->ev_part_in[b][part], 0));

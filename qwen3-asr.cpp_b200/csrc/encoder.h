@@ -16,7 +16,7 @@ struct q3a_encoder {
     // download (copy_out), staging buffers double-buffered by pass parity
     cudaStream_t copy_in = nullptr, copy_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
-    static constexpr int kInParts = 4, kOutParts = 2;   // finer overlap inside a pass (PartHooks in encoder.cu)
+    static constexpr int kInParts = 4, kOutParts = 4;   // upper bounds; the split tables choose   // finer overlap inside a pass (PartHooks in encoder.cu)
     cudaEvent_t ev_part_in[2][kInParts] = {}, ev_part_out[2][kOutParts] = {};
 
     // ---- weights (one arena) -----------------------------------------------------------------

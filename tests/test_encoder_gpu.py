@@ -229,6 +229,24 @@ def test_copy_overlap_partitions_do_not_change_results(lib, asr_model, monkeypat
     enc.close(); fe.close()
 
 
+def test_no_kernel_writes_outside_its_buffers(lib, tiny_models, asr_model):
+    """The library's own bounds check (compute-sanitizer is not available on this pool): in a child process with
+    Q3A_GUARD=1 every device buffer is exact-size between two pattern bands; tests/guard_battery.py drives every
+    entry point over ragged / empty / multi-part inputs and no band may change."""
+    import json, subprocess, sys
+    _, models = tiny_models
+    _, paths, _ = asr_model
+    env = dict(os.environ, Q3A_GUARD="1")
+    r = subprocess.run([sys.executable, os.path.join(os.path.dirname(__file__), "guard_battery.py"),
+                        models["f16"][0], models["q8_0"][0], paths["f16"]], env=env, capture_output=True, text=True, timeout=900)
+    assert r.stdout.strip(), r.stderr[-2000:]
+    rep = json.loads(r.stdout.strip().splitlines()[-1])
+    assert rep["damaged"] == 0, rep["msg"]
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert rep["bands"] >= 100 and rep["cases"] >= 50, rep
+    assert rep["selftest_damaged"] == 1, rep                   # the detector fires on a deliberate one-byte overrun
+
+
 def test_int16_ingest_matches_load_wav_conversion(lib, tiny_models):
     """q3a_encode_pcm16_batch = load_wav's int16 -> float conversion (mel_spectrogram.cpp:195-210) + the float path:
     mono and interleaved stereo, bit-identical to converting on the host the way the reference does."""
