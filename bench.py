@@ -188,6 +188,9 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU arm)")
+    from q3a_b200 import hostbind
+    # before any pinned allocation: buffers land on the GPU's NUMA node (Q3A_BENCH_NO_BIND=1 for an A/B run)
+    binding_info = {"bound": False, "why_not": "Q3A_BENCH_NO_BIND"} if os.environ.get("Q3A_BENCH_NO_BIND") else hostbind.bind_to_gpu(local)
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -330,6 +333,7 @@ def run_ours(args):
                 "api": "q3a_encode_pcm_batch (pinned host PCM -> pinned host features)"},
         "gpu_launches": launches0,
         "clocks": clocks,
+        "host_binding": binding_info,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM: conv2/conv3 implicit GEMM + all Linear layers)",
                      "achieved": gemm_tf, "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": gemm_tf / pk["tflops_sustained"],
                      "traffic": traffic, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
