@@ -43,6 +43,28 @@ def test_tiny_tower_matches_oracle(lib, tiny_models, filters, ftype, opd, mode, 
     enc.close()
 
 
+@pytest.mark.parametrize("mode,variant", [(B.MODE_ASR, "asr"), (B.MODE_ALIGNER, "aligner")])
+def test_ten_minute_clip(lib, tiny_models, filters, mode, variant):
+    """One 10-minute utterance (600 chunks + a 37-frame tail, 7805 tokens): in ASR mode a single full-attention
+    sequence of 61 query tiles x 122 key blocks per head (the K/V ring and the lazy rescale wrap many times), in aligner
+    mode 76 windows of 104 tokens.  The reference has no length limit on this path (audio_encoder.cpp:312-354)."""
+    shape, models = tiny_models
+    path, W = models["f16"]
+    enc = B.Encoder(path, 0, B.OP_F16)
+    fe = B.Frontend(0)
+    pcm = synth.synth_audio(77, 16000 * 600 + 37 * 160 + 11)
+    mel = MO.log_mel_numpy(pcm, filters)
+    want = _oracle(mel, W, shape, variant)
+    got = enc.encode_batch([mel], mode)[0]
+    assert got.shape == want.shape == (synth.chunk_tokens(mel.shape[1]), shape.out_dim)
+    cos, rel = compare(got, want)
+    assert cos >= COS and rel <= REL, (cos, rel)
+    fused = enc.encode_pcm_batch(fe, [pcm], mode)[0]           # PCM in: mel on the device, clamp fused into conv1
+    cos, rel = compare(fused, want)
+    assert cos >= COS and rel <= REL, (cos, rel)
+    enc.close(); fe.close()
+
+
 def test_tiny_q8_file_matches_oracle(lib, tiny_models, filters):
     """Q8_0 file: conv kernels stay F16, Linear weights are Q8_0 blocks (convert_hf_to_gguf.py:303-308).  The
     oracle also quantises activations to Q8_0 (ggml's vec_dot_type); on this 128-wide toy tower that noise
