@@ -7,7 +7,7 @@ from q3a_b200 import binding as B
 
 lib = B.load()
 torch.manual_seed(0)
-H, L, NS = 14, 390, 64
+H, L, NS = 14, int(os.environ.get('ATTN_L', 390)), int(os.environ.get('ATTN_NS', 64))
 cu = [i * L for i in range(NS + 1)]
 T = cu[-1]
 qkv = (torch.randn(T, 3 * H * 64, device="cuda") * 1.5).to(torch.bfloat16)
@@ -23,7 +23,7 @@ for it in range(12):
     times.append(e0.elapsed_time(e1) * 1e3)
 flops = 4.0 * 64 * H * NS * L * L
 best = min(times[2:])
-print(f"attention 64x390 H=14: best {best:.1f} us ({flops / best / 1e6:.0f} TFLOP/s), all {[round(t) for t in times]}")
+print(f"attention {NS}x{L} H=14 ({NS * ((L + 127) // 128) * H} CTAs, {(L + 63) // 64} key blocks): best {best:.1f} us ({flops / best / 1e6:.0f} TFLOP/s), all {[round(t) for t in times]}")
 # correctness on one segment
 q, k, v = [x.float().view(T, H, 64) for x in qkv.split(H * 64, dim=1)]
 s = slice(0, L)
