@@ -9,19 +9,21 @@
 // One CTA (128 threads, one query row per thread) = one (128-query tile, head); keys go in blocks of KT = 64
 // (three CTAs per SM; KT = 128 with two CTAs per SM is kept behind Q3A_ATTN_KT=128).
 // Per key block j:
-//   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,KT); issued one block ahead, so it runs
-//                            while the threads are still busy with block j-1
+//   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,KT)
 //   S_j -> registers         tcgen05.ld.x32 back to back, one wait
 //   softmax                  row maximum (four chains), p = exp2(s*scale - m) with a lazily updated reference
 //                            maximum m (O in TMEM is rescaled only when the row maximum grows by more than 2^8,
 //                            so the common block never reads O back), row sum in fp32, P packed in place
-//   P_j -> smem (16-bit, 128-byte swizzled K-major), O += P_j V_j   tcgen05.mma accumulating in TMEM
-//                            columns [KT,KT+64); V is the MN-major B operand
-// K and V blocks are double-buffered with separate barriers: K_{j+2} is fetched as soon as Q K_j^T has
-// retired, V_{j+1} as soon as P_{j-1} V_{j-1} has.  Warp 0 doubles as the issue warp and stays converged
-// (elect.sync around the TMA / MMA instructions only).  Warps whose 32 query rows all lie past the end of the
-// segment skip the softmax arithmetic.  The epilogue divides by the row sum, transposes through the idle Q tile
-// and stores whole 128-byte rows.  DESIGN.md 4.2 has the measurements behind each of these choices.
+//   P_j -> TMEM              tcgen05.st over the row's own consumed scores, two 16-bit values per column
+//   O += P_j V_j             tcgen05.mma with the A operand read from TMEM, accumulating in columns [KT,KT+64);
+//                            V is the MN-major B operand.  Q K_{j+1}^T is issued right behind it: the pipe executes
+//                            in order, so S_{j+1} overwrites P_j only after P_j V_j has read it, and it completes
+//                            while the other CTAs of the SM run their softmax
+// One bar.sync per block (P written -> issue).  K and V blocks are double-buffered with separate barriers: K_{j+2} is
+// fetched as soon as Q K_j^T has retired, V_{j+1} as soon as P_{j-1} V_{j-1} has.  Warp 0 doubles as the issue warp and
+// stays converged (elect.sync around the TMA / MMA instructions only).  Warps whose 32 query rows all lie past the
+// end of the segment skip the softmax arithmetic.  The epilogue divides by the row sum, transposes through the idle
+// Q tile and stores whole 128-byte rows.  DESIGN.md 4.2 has the measurements behind each of these choices.
 #include "attention.h"
 #include "tc.cuh"
 #include "tmap.h"
@@ -33,15 +35,17 @@ namespace q3a {
 constexpr int kHd = 64;
 constexpr int kQT = 128;                 // queries per CTA
 constexpr int kTileBytes = 128 * 64 * 2; // 16 KB: [128 rows][64 x 16-bit]
-// KT = keys per block (128 or 64).  128: fewer blocks, 2 CTAs/SM (255 registers, 112 KB smem, 256 TMEM columns).
-// 64: half the per-thread state, so 3 CTAs/SM fit (168 registers, 64 KB, 128 columns) and hide each other's
-// barrier / TMEM-load latency better.
+// KT = keys per block (128 or 64).  128: fewer blocks, 2 CTAs/SM (227 registers, 80 KB smem, 256 TMEM columns).
+// 64: half the per-thread state, so 3 CTAs/SM fit (157 registers, 48 KB, 128 columns) and hide each other's
+// barrier / TMEM-load latency better.  (A fourth CTA would need 128 registers: 384 B of spills.)
+#ifndef Q3A_ATTN_CTAS
+#define Q3A_ATTN_CTAS 3
+#endif
 template <int KT> struct AttnCfg {
     static constexpr int kKV = KT * 64 * 2;                    // one K or V block
-    static constexpr int kP = 128 * KT * 2;                    // P: KT/64 sub-tiles of [128][64]
-    static constexpr int kSmem = kTileBytes + 4 * kKV + kP + 128;
+    static constexpr int kSmem = kTileBytes + 4 * kKV + 128;   // Q, 2 x K, 2 x V, barriers (P lives in TMEM)
     static constexpr int kTmemCols = KT == 128 ? 256 : 128;    // S: columns [0,KT), O: columns [KT,KT+64)
-    static constexpr int kCtas = KT == 128 ? 2 : 3;
+    static constexpr int kCtas = KT == 128 ? 2 : Q3A_ATTN_CTAS;
 };
 constexpr float kRescaleThreshold = 8.0f;   // log2 units: p <= 2^8 between rescales
 
@@ -58,9 +62,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     const uint32_t sQ = base;
     auto sK = [&](int b) { return base + kTileBytes + kKV * b; };
     auto sV = [&](int b) { return base + kTileBytes + kKV * (2 + b); };
-    constexpr int kPOff = kTileBytes + 4 * kKV, kBarOff = kPOff + Cfg::kP;
-    const uint32_t sP = base + kPOff;
-    uint8_t* gP = smem_raw + kPOff;
+    constexpr int kBarOff = kTileBytes + 4 * kKV;
     const uint32_t bars = base + kBarOff;
     const uint32_t bar_q = bars, bar_s = bars + 8, bar_o = bars + 16;
     auto bar_k = [&](int b) { return bars + 24 + 8 * b; };
@@ -151,18 +153,12 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
                 if (c * 32 < nk) tc::tmem_ld_32x32b_x32(t_row + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&s[c * 32]));
             tc::tmem_ld_wait();
         }
-        tc::fence_before_sync();
-        __syncthreads();                                   // S is in registers everywhere: TMEM S and K_j are free
-        if (warp == 0) {
-            tc::fence_after_sync();
-            if (j + 2 < nkv) {
-                if (tc::elect_one()) {
-                    tc::mbar_arrive_expect_tx(bar_k(j & 1), kKV);
-                    tc::tma_load_2d(sK(j & 1), &tmap_kv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
-                }
-                __syncwarp();
+        if (warp == 0 && j + 2 < nkv) {                    // Q K_j^T has retired: its K buffer is free
+            if (tc::elect_one()) {
+                tc::mbar_arrive_expect_tx(bar_k(j & 1), kKV);
+                tc::tma_load_2d(sK(j & 1), &tmap_kv, bar_k(j & 1), col_k, t.seg_start + (j + 2) * kKT);
             }
-            if (j + 1 < nkv) issue_qk(j + 1);
+            __syncwarp();
         }
         // ---- softmax on registers -------------------------------------------------------------------
         float psum = 0.0f;
@@ -243,25 +239,16 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
             }
             l_run += psum;
         }
-        // ---- P_j -> smem once P_{j-1} V_{j-1} has retired (it read the P buffer and V_{j-1}) ------------
+        // every thread follows the O barrier phase by phase (the epilogue's parity wait relies on it); P V_{j-1} retired
+        // long ago, and with it V_{j-1}'s buffer is free
         if (j > 0) { tc::mbar_wait(bar_o, (j - 1) & 1); tc::fence_after_sync(); }
+        // ---- P_j -> TMEM, over this row's consumed scores (two 16-bit values per column): the A operand of P V ----
         if (row_live) {
-            // 64-key sub-tile c, 16-byte chunks XOR-swizzled with row % 8
 #pragma unroll
-            for (int c = 0; c < kKT / 64; ++c) {
-                if (c * 64 < nk) {
-                    uint8_t* prow = gP + c * kTileBytes + tid * 128;
-#pragma unroll
-                    for (int g = 0; g < 8; ++g) {
-                        if (c * 64 + g * 8 >= nk) break;
-                        uint4 u = make_uint4(pk[c * 32 + g * 4 + 0], pk[c * 32 + g * 4 + 1], pk[c * 32 + g * 4 + 2],
-                                             pk[c * 32 + g * 4 + 3]);
-                        *reinterpret_cast<uint4*>(prow + ((g ^ (tid & 7)) << 4)) = u;
-                    }
-                }
-            }
+            for (int c = 0; c < kKT / 64; ++c)
+                if (c * 64 < nk) tc::tmem_st_32x32b_x32(t_row + c * 32, *reinterpret_cast<uint32_t(*)[32]>(&pk[c * 32]));
+            tc::tmem_st_wait();
         }
-        tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the tensor core
         tc::fence_before_sync();
         __syncthreads();
         if (warp == 0) {
@@ -278,16 +265,15 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
             tc::fence_after_sync();
             const uint32_t idesc = tc::make_idesc(kFmt, kQT, kHd, 0, 1);
             const uint64_t b0 = tc::smem_desc_mnmajor_sw128(sV(j & 1));
-            const uint64_t a0 = tc::smem_desc_kmajor_sw128(sP), a1 = tc::smem_desc_kmajor_sw128(sP + kTileBytes);
             const int ks = nk / 16;
             if (tc::elect_one()) {
 #pragma unroll
-                for (int k = 0; k < kKT / 16; ++k)          // 16 key rows of V = 2048 B
-                    if (k < ks) tc::mma_f16_ss(tmem + kKT, (k < 4 ? a0 : a1) + 2 * (k & 3), b0 + (uint64_t)k * 128, idesc,
-                                               (j | k) != 0);
+                for (int k = 0; k < kKT / 16; ++k)          // 16 keys: 8 columns of P, 16 rows of V = 2048 B
+                    if (k < ks) tc::mma_f16_ts(tmem + kKT, tmem + 8 * k, b0 + (uint64_t)k * 128, idesc, (j | k) != 0);
                 tc::mma_commit(bar_o);
             }
             __syncwarp();
+            if (j + 1 < nkv) issue_qk(j + 1);               // behind P V in the pipe: S_{j+1} overwrites P_j only after it was read
         }
     }
 
