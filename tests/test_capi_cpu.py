@@ -119,3 +119,17 @@ def test_host_call_schedule(lib):
     assert B.plan_host_call([], B.MODE_ASR) == ([], [], [])
     with pytest.raises(B.Q3AError):
         B.plan_host_call([-1], B.MODE_ASR)
+
+
+def test_host_binding_never_raises_and_never_widens():
+    """hostbind.bind_to_gpu is an optimisation for multi-socket hosts: without NVML (this container) it reports why it
+    did nothing, and it can only ever shrink the set of CPUs the process may run on."""
+    import os
+    from q3a_b200 import hostbind
+    before = os.sched_getaffinity(0)
+    info = hostbind.bind_to_gpu(0)
+    after = os.sched_getaffinity(0)
+    assert after <= before and len(after) > 0
+    assert info["bound"] == (after != before)
+    assert info["cpus"] == len(after)
+    os.sched_setaffinity(0, before)
