@@ -34,6 +34,19 @@ SR = 16000
 ASR_GFLOP_PER_30S = 278.02
 
 
+def headline_config():
+    """The workload both arms are quoted on (BASELINE.json configs[1]); the CPU arm times a bounded sample of it."""
+    T = 390 * BATCH
+    return {"workload": "qwen3-asr-0.6b mel+encoder, batch of 64 x 30-s synthetic 16 kHz clips per GPU "
+                        "(BASELINE.json configs[1]), random-init weights via GGUF F16",
+            "batch_clips": BATCH, "clip_seconds": CLIP_SECONDS, "tokens_per_step": T, "mode": "asr (full attention)",
+            "l2": "two PCM input sets alternated (246 MB > L2); a step streams ~8 GB of workspace",
+            "algorithmic_gflop_per_step": ASR_GFLOP_PER_30S * BATCH}
+
+
+CPU_SAMPLE_CLIPS = 2          # 30-s clips of the headline workload per CPU step (both the cpu_baseline leg and --impl reference)
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -152,10 +165,12 @@ def run_reference(args):
     if rank != 0:
         return
     total = args.steps + args.warmup
-    cores = os.cpu_count() or 1
-    # bounded: a 30-s clip costs ~3 s of mel (one thread) + ~3 s of encoder; keep the whole run within a few minutes
-    clip_s = 30.0 if total <= 16 else (10.0 if total <= 48 else 5.0)
-    per_step = max(1, min(cores, 4 if total <= 6 else 2))
+    # One stated sample for both CPU figures: CPU_SAMPLE_CLIPS 30-s clips of the headline workload per step (a clip
+    # costs ~3 s of mel on one thread + ~3 s of encoder on all cores); 1 clip per step for long runs so that the whole
+    # --steps K --warmup W run ends within a few minutes.  The per-clip rate does not depend on the batch size: the
+    # reference encodes one utterance at a time (qwen3_asr.cpp:81-149).
+    clip_s = float(CLIP_SECONDS)
+    per_step = CPU_SAMPLE_CLIPS if total <= 20 else 1
     t_all = time.perf_counter()
     secs = mel = 0.0
     for i in range(total):
@@ -164,11 +179,11 @@ def run_reference(args):
             secs += a; mel += b
     value = args.steps * per_step * clip_s / secs
     desc = _cpu_desc(args.steps * per_step, clip_s, mel, secs - mel)
+    desc["sample"] = f"{per_step} of the workload's 64 x 30-s clips per step; " + desc["sample"]
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(args.steps, 1), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f16 weights, f32/f64 arithmetic", "data": "synthetic",
-            "config": {"workload": f"qwen3-asr-0.6b mel+encoder, {per_step} x {clip_s:g}-s synthetic clips per step, CPU host cores",
-                       "clip_seconds": clip_s, "clips_per_step": per_step},
+            "config": headline_config(),
             "cpu_baseline": {"value": value, "unit": UNIT, **desc},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0, "wall_s": time.perf_counter() - t_all}
@@ -279,6 +294,24 @@ def run_ours(args):
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     e2e_value = audio_s / float(dt.item())
 
+    # ---- the timed device-resident call is checked, not just timed: its output must equal, bit for bit, what the
+    #      (tested) host-pointer call returns for the same input set (batch-invariant kernels, same code underneath)
+    step_e2e(0)
+    out_dev.fill_(float("nan"))
+    step_dev(0)
+    torch.cuda.synchronize()
+    got = out_dev.cpu()
+    want = torch.cat(out_host, dim=0)
+    finite = bool(torch.isfinite(got).all())
+    max_diff = float((got - want).abs().max()) if finite else float("nan")
+    ok = torch.tensor([1 if (finite and torch.equal(got, want)) else 0], device="cuda")
+    if world > 1:
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    value_checked = bool(ok.item())
+    if not value_checked:
+        raise SystemExit(f"bench.py: q3a_encode_pcm_device output differs from q3a_encode_pcm_batch on rank {rank} "
+                         f"(finite={finite}, max |diff| = {max_diff}) -- the timed value is void")
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -302,41 +335,46 @@ def run_ours(args):
     mel_gbs = mel_bytes / (mel_ms / 1e3) / 1e9
     # DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum), from the committed launch list of this
     # same workload (profiles/roofline_traffic.json, written by scripts/summarize_profile.py); null without it
-    traffic = traffic_attn = traffic_mel = None
+    traffic = traffic_attn = traffic_mel = traffic_note = None
     tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tp):
         try:
             with open(tp) as f:
                 tj = json.load(f)
-            traffic = tj.get("gemm_tc_kernel_dram_bytes_per_launch")
-            traffic_attn = tj.get("attention_kernel_dram_bytes_per_launch")
-            traffic_mel = tj.get("mel_frames_kernel_dram_bytes_per_launch")
+            import importlib.util
+            spec = importlib.util.spec_from_file_location("q3a_build", os.path.join(ROOT, "qwen3-asr.cpp_b200", "build.py"))
+            bmod = importlib.util.module_from_spec(spec); spec.loader.exec_module(bmod)
+            if tj.get("csrc_sha256") == bmod.source_hash():      # the ncu capture was taken from these very sources
+                traffic = tj.get("gemm_tc_kernel_dram_bytes_per_launch")
+                traffic_attn = tj.get("attention_kernel_dram_bytes_per_launch")
+                traffic_mel = tj.get("mel_frames_kernel_dram_bytes_per_launch")
+            else:
+                traffic_note = "profiles/roofline_traffic.json is from other sources (csrc hash mismatch): traffic not reported"
         except Exception:
             pass
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        v, desc = cpu_path_rate(30.0, 4)
+        v, desc = cpu_path_rate(float(CLIP_SECONDS), CPU_SAMPLE_CLIPS)
+        desc["sample"] = f"{CPU_SAMPLE_CLIPS} of the workload's 64 x 30-s clips; " + desc["sample"]
         cpu = {"value": v, "unit": UNIT, **desc}
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "bf16 operands, fp32 accumulate (mel: fp32)", "data": "synthetic",
-        "config": {"workload": "qwen3-asr-0.6b mel+encoder, batch of 64 x 30-s synthetic 16 kHz clips per GPU "
-                               "(BASELINE.json configs[1]), random-init weights via GGUF F16",
-                   "batch_clips": BATCH, "clip_seconds": CLIP_SECONDS, "tokens_per_step": T, "mode": "asr (full attention)",
-                   "l2": "two PCM input sets alternated (246 MB > L2); a step streams ~8 GB of workspace",
-                   "algorithmic_gflop_per_step": ASR_GFLOP_PER_30S * BATCH},
+        "config": headline_config(),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": BATCH * n * 4,
                 "d2h_bytes_per_step": T * enc.hp.out_dim * 4, "timer": "host wall clock around K synchronous C-ABI calls, max over ranks",
                 "api": "q3a_encode_pcm_batch (pinned host PCM -> pinned host features)"},
         "gpu_launches": launches0,
+        "value_checked": value_checked, "value_check": {"against": "q3a_encode_pcm_batch on the same 64 clips (host result)",
+                                                         "max_abs_diff": max_diff, "rows": int(got.shape[0])},
         "clocks": clocks,
         "host_binding": binding_info,
         "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05 GEMM: conv2/conv3 implicit GEMM + all Linear layers)",
                      "achieved": gemm_tf, "peak": pk["tflops_sustained"], "unit": "TFLOP/s", "frac": gemm_tf / pk["tflops_sustained"],
-                     "traffic": traffic, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                     "traffic": traffic, "traffic_note": traffic_note, "peak_source": pk["source"] + ", sustained bf16 (kernel timed inside a long step)",
                      "launches_per_step": g_n // max(args.steps, 1), "ms_per_step": g_ms / args.steps,
                      "how": "algorithmic FLOPs (2*M*N*K, no padding) / CUDA-event time of every launch, separate profiled pass of the same K steps"},
         "roofline_attention": {"bound": "tensor", "kernel": "attention_kernel (tcgen05 varlen attention)",

@@ -123,7 +123,14 @@ int q3a_mel_batch_device(q3a_frontend* fe, const float* pcm_dev, const int64_t* 
 /* replaces AudioEncoder::load_model (audio_encoder.h:25, audio_encoder.cpp:42-83) and the aligner's
  * private loader (forced_aligner.cpp:177-475): reads the audio.encoder.* tensors of a GGUF file
  * (F32 / F16 / Q8_0), takes hyper-parameters from the qwen3-asr.* keys the converter writes
- * (convert_hf_to_gguf.py:441-447) and falls back to tensor shapes / the reference defaults. */
+ * (convert_hf_to_gguf.py:441-447) and falls back to tensor shapes / the reference defaults.
+ * Supported shapes (both reference presets fit; anything else fails with Q3A_ERR_FORMAT): 128 mel bins,
+ * head_dim 64 (d_model = 64 * heads), d_model <= 1024, every dimension a multiple of 8, n_window_infer = 800
+ * (104-token windows); layer_norm_eps and n_window_infer are read from "audio.layer_norm_eps" /
+ * "audio.n_window_infer" like the reference's loader does (gguf_loader.cpp:76-77), default 1e-5 / 800.
+ * Every tensor the reference's graph uses must be present (all biases, ln_post, proj1/2): the reference treats them
+ * as optional, this loader does not.  Q8_0 files: Linear weights stay Q8_0 blocks in device memory and are
+ * dequantised inside the GEMM's producer (Q3A_Q8_DEQUANT_AT_LOAD=1 in the environment expands them at load instead). */
 int q3a_encoder_load(const char* gguf_path, int device, int operand_dtype, q3a_encoder** out);
 void q3a_encoder_free(q3a_encoder* enc);
 int q3a_encoder_get_hparams(const q3a_encoder* enc, q3a_hparams* out);
@@ -140,7 +147,8 @@ int q3a_encoder_encode_batch(q3a_encoder* enc, const float* const* mel, int n_me
 /* device-resident variant: mel_dev packed as produced by q3a_mel_batch_device (finalize=1), or raw
  * log-mel plus max_dev (finalize=0; the clamp and scale are then applied inside conv1's loads).
  * out_dev: [sum n_tokens][out_dim] f32, utterances in order.  tok_off (host, n_utts+1, may be NULL)
- * receives the row offsets. */
+ * receives the row offsets.  mel_dev / out_dev must be 16-byte aligned, mel_off entries multiples of 4.
+ * Asynchronous on `stream`; the host arrays may be reused as soon as the call returns. */
 int q3a_encoder_encode_device(q3a_encoder* enc, const float* mel_dev, const int64_t* mel_off,
                               const float* max_dev, const int* n_frames, int n_utts, int mode,
                               float* out_dev, int64_t* tok_off, void* stream);
@@ -155,7 +163,9 @@ int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* enc, const float* const*
  * Results are bit-identical to q3a_encode_pcm_batch on load_wav's float output. */
 int q3a_encode_pcm16_batch(q3a_frontend* fe, q3a_encoder* enc, const int16_t* const* pcm, const int* n_samples,
                            int n_channels, int n_clips, int mode, float* const* out, int* n_tokens);
-/* same with PCM and features resident on the device (packed as above). */
+/* same with PCM and features resident on the device (packed as above): pcm_dev / out_dev 16-byte aligned, pcm_off
+ * entries multiples of 4.  Asynchronous on `stream`.  This is the hand-off a GPU-resident decoder consumes: the rows are
+ * the memory text_decoder.cpp:422-456,650-655 copies into inp_audio. */
 int q3a_encode_pcm_device(q3a_frontend* fe, q3a_encoder* enc, const float* pcm_dev, const int64_t* pcm_off,
                           const int* n_samples, int n_clips, int mode, float* out_dev, int64_t* tok_off,
                           void* stream);

@@ -33,6 +33,18 @@ def headers() -> list[str]:
     return hs
 
 
+def source_hash() -> str:
+    """sha256 over the kernel sources (csrc/* and include/q3a.h, names + contents): ties a committed profile to the
+    build it was taken from (profiles/roofline_traffic.json carries it; bench.py prints traffic: null on mismatch)."""
+    import hashlib
+    h = hashlib.sha256()
+    for path in sorted(sources() + headers()):
+        h.update(os.path.basename(path).encode())
+        with open(path, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def _stale(target: str, deps: list[str]) -> bool:
     if not os.path.exists(target):
         return True
@@ -78,4 +90,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
+    if "--hash" in sys.argv:
+        print(source_hash())
+        sys.exit(0)
     print(build(force="--force" in sys.argv, verbose="--verbose" in sys.argv))

@@ -264,12 +264,14 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         Q3A_CUDA(cudaMemsetAsync(e->planes1.p, 0, (size_t)4 * cap * F2 * C * 2, st));
         e->rcap1 = cap; e->sigP2 = P2;
     }
-    if (r2 > e->rcap2 || P3 != e->sigP3) {
+    // planes2's pad rows depend on P2 as well: conv2 writes ot <= P2-2, so for an even P2 the last odd-time row of every
+    // chunk (read by conv3 as zero padding) is never written, while an odd P2 with the same P3 fills it with data
+    if (r2 > e->rcap2 || P3 != e->sigP3 || P2 != e->sigP2_planes2) {
         const int cap = std::max(r2 + r2 / 4, e->rcap2);
         Q3A_CUDA(cudaStreamSynchronize(st));
         Q3A_TRY(e->planes2.reserve((size_t)4 * cap * F3 * C * 2));
         Q3A_CUDA(cudaMemsetAsync(e->planes2.p, 0, (size_t)4 * cap * F3 * C * 2, st));
-        e->rcap2 = cap; e->sigP3 = P3;
+        e->rcap2 = cap; e->sigP3 = P3; e->sigP2_planes2 = P2;
     }
     const int feat_dim = F3 * C;
     Q3A_TRY(e->feat.reserve((size_t)T * feat_dim * 2));
@@ -461,8 +463,11 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
     hp.n_mel_bins = (int)f.get_u32(A + "num_mel_bins", 128);
     hp.conv_channels = (int)f.get_u32(A + "conv_channels", (uint32_t)t_c1->ne[3]);
     hp.conv_out_dim = hp.d_model;
-    hp.n_window_infer = 800;
-    hp.layer_norm_eps = 1e-5f;
+    // the reference's loader reads these two under its own key names with the same defaults (gguf_loader.cpp:76-77);
+    // the converter writes neither.  The window length must be the 800 the attention windows are built for.
+    hp.n_window_infer = (int)f.get_u32("audio.n_window_infer", 800);
+    hp.layer_norm_eps = f.get_f32("audio.layer_norm_eps", 1e-5f);
+    if (hp.n_window_infer != 800) { set_error("only n_window_infer = 800 (104-token attention windows) is supported"); return Q3A_ERR_FORMAT; }
     hp.out_dim = (int)t_p2->ne[1];
     hp.weight_ftype = (int)t_up->type;
     const int d = hp.d_model, C = hp.conv_channels, ffn = hp.ffn_dim, F3 = hp.n_mel_bins / 8;
@@ -652,6 +657,9 @@ extern "C" int q3a_encoder_encode_device(q3a_encoder* e, const float* mel_dev, c
                                          float* out_dev, int64_t* tok_off, void* stream) {
     if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
     if (n_utts < 0 || (n_utts > 0 && (!mel_dev || !mel_off || !n_frames || !out_dev))) { set_error("encode_device: null argument"); return Q3A_ERR_ARG; }
+    if ((reinterpret_cast<uintptr_t>(mel_dev) & 15u) || (reinterpret_cast<uintptr_t>(out_dev) & 15u)) {
+        set_error("encode_device: mel_dev and out_dev must be 16-byte aligned"); return Q3A_ERR_ARG;
+    }
     Q3A_TRY(use_device(e->device));
     g_launch_counter = 0;
     prof_reset(e);
@@ -930,6 +938,11 @@ extern "C" int q3a_encode_pcm_device(q3a_frontend* fe, q3a_encoder* e, const flo
     if (!e || !fe) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
     if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
     if (n_clips < 0 || (n_clips > 0 && (!pcm_dev || !pcm_off || !n_samples || !out_dev))) { set_error("encode_pcm_device: null argument"); return Q3A_ERR_ARG; }
+    if ((reinterpret_cast<uintptr_t>(pcm_dev) & 15u) || (reinterpret_cast<uintptr_t>(out_dev) & 15u)) {
+        set_error("encode_pcm_device: pcm_dev and out_dev must be 16-byte aligned (bulk copies / TMA)"); return Q3A_ERR_ARG;
+    }
+    for (int i = 0; i < n_clips; ++i)
+        if (pcm_off[i] < 0 || (pcm_off[i] & 3)) { set_error("encode_pcm_device: pcm_off entries must be non-negative multiples of 4"); return Q3A_ERR_ARG; }
     Q3A_TRY(use_device(e->device));
     g_launch_counter = 0;
     prof_reset(e);

@@ -37,7 +37,7 @@ struct q3a_encoder {
 
     // ---- workspace (grows, never shrinks) -----------------------------------------------------
     q3a::DevBuf planes1, planes2, feat, x, h, qkv, att, up, tables, stage_in, stage_out, stage_in2, stage_out2, stage_pcm, stage_mel, stage_max;
-    int rcap1 = 0, rcap2 = 0, sigP2 = 0, sigP3 = 0;   // plane layout the zero rows were prepared for
+    int rcap1 = 0, rcap2 = 0, sigP2 = 0, sigP3 = 0, sigP2_planes2 = 0;   // plane layout the zero rows were prepared for
     q3a::PinnedRing ring;
 
     // ---- profiling ------------------------------------------------------------------------------

@@ -92,6 +92,10 @@ def launches(tag: str) -> None:
         with open(os.path.join(PROF, "roofline_traffic.json"), "w") as f:       # read by bench.py -> roofline.traffic
             out = {"gemm_tc_kernel_dram_bytes_per_launch": g["dram_bytes"] / g["launches"], "launches_per_step": g["launches"],
                    "source": f"profiles/{tag}_traffic.json"}
+            # hash of csrc/ as it was on the GPU box when the launch list was taken (the gpurun script writes it next to
+            # the csv); bench.py reports traffic only while the sources it runs still hash to this
+            hp = os.path.join(GO, "csrc_sha256.txt")
+            out["csrc_sha256"] = open(hp).read().strip() if os.path.exists(hp) else None
             for fam in ("attention_kernel", "mel_frames_kernel"):
                 t = traffic.get(fam)
                 if t and t["launches"]:

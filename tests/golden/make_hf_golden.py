@@ -15,7 +15,11 @@ mask to the layers (every token attends to every token -- what AudioEncoder::enc
 with flash attention the cu_seqlens of 104-token windows apply (what ForcedAligner::encode_audio does,
 forced_aligner.cpp:737-766).  "full_*" is the former, "win_*" the latter (through the block mask the class itself builds).
 
-    python tests/golden/make_hf_golden.py        # needs transformers (>= 4.57) and torch, CPU only; writes hf_audio_tower_tiny.npz
+Real widths (hf_audio_tower_wide.npz): the same generator on 2-layer towers with the production widths -- ASR
+(d = 896, 14 heads, ffn 3584, conv 480: GEMM tiles BLOCK_N 224 / 256 / 240) and aligner (d = 1024, 16 heads, ffn 4096) --
+so that the CUDA tile paths those widths select are pinned to upstream outputs too, not only to our own restatement.
+
+    python tests/golden/make_hf_golden.py        # needs transformers (>= 4.57) and torch, CPU only; writes both .npz files
 """
 from __future__ import annotations
 
@@ -70,13 +74,19 @@ def build_tower(shape: synth.EncoderShape, weights: dict[str, np.ndarray]):
     return tower
 
 
-def main() -> None:
-    shape = synth.tiny_shape()
-    weights = synth.random_weights(shape, 7)
+# 2-layer towers at the production widths (tests/test_encoder_gpu.py builds the same weights from the same seeds)
+WIDE = {
+    "asr": (synth.EncoderShape("asr-2l", 2, 896, 14, 3584), 21),
+    "aligner": (synth.EncoderShape("aligner-2l", 2, 1024, 16, 4096), 22),
+}
+WIDE_CLIPS = ((114, 16000 * 2 + 4321), (115, 16000 * 11 + 77), (116, 100 * 160 * 3))
+
+
+def run_tower(shape, weights, clips, prefix=""):
     tower = build_tower(shape, weights)
     filt = np.load(os.path.join(HERE, "mel_ref.npz"))["filters"]           # the reference's own filterbank
     out = {}
-    for seed, n in ((104, 16000 * 2 + 4321), (105, 16000 * 11 + 77), (106, 100 * 160 * 3)):
+    for seed, n in clips:
         mel = MO.log_mel_numpy(synth.synth_audio(seed, n), filt)
         captured = {}
         hook = tower.layers[0].register_forward_pre_hook(
@@ -93,11 +103,22 @@ def main() -> None:
             for layer in tower.layers:
                 h = layer(h, cu, attention_mask=mask)[0]
             h = tower.proj2(tower.act(tower.proj1(tower.ln_post(h))))
-        out[f"full_{seed}_{n}"] = y.last_hidden_state.numpy().astype(np.float32)
-        out[f"win_{seed}_{n}"] = h.numpy().astype(np.float32)
-        out[f"cu_{seed}_{n}"] = cu.numpy().astype(np.int64)
-        print(seed, n, mel.shape, out[f"full_{seed}_{n}"].shape, cu.tolist())
+        if not prefix or mel.shape[1] % 100 == 0:      # wide file: the eager reading only where ASR mode is the same graph
+            out[f"{prefix}full_{seed}_{n}"] = y.last_hidden_state.numpy().astype(np.float32)
+        out[f"{prefix}win_{seed}_{n}"] = h.numpy().astype(np.float32)
+        out[f"{prefix}cu_{seed}_{n}"] = cu.numpy().astype(np.int64)
+        print(prefix, seed, n, mel.shape, out[f"{prefix}win_{seed}_{n}"].shape, cu.tolist())
+    return out
+
+
+def main() -> None:
+    shape = synth.tiny_shape()
+    out = run_tower(shape, synth.random_weights(shape, 7), ((104, 16000 * 2 + 4321), (105, 16000 * 11 + 77), (106, 100 * 160 * 3)))
     np.savez_compressed(os.path.join(HERE, "hf_audio_tower_tiny.npz"), **out)
+    wide = {}
+    for name, (shape, seed) in WIDE.items():
+        wide.update(run_tower(shape, synth.random_weights(shape, seed), WIDE_CLIPS, prefix=name + "."))
+    np.savez_compressed(os.path.join(HERE, "hf_audio_tower_wide.npz"), **wide)
 
 
 if __name__ == "__main__":

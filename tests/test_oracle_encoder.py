@@ -130,3 +130,30 @@ def test_graph_matches_upstream_hf_audio_tower():
         # the price of ggml's tanh-form GELU (audio_encoder.cpp:112 -> ggml_gelu) against the upstream erf form
         tanh = EO.encode(mel, W, variant="aligner", nm=EO.IDEAL, **kw)
         assert np.abs(tanh - g[key]).max() <= 1e-3 * np.abs(g[key]).max()
+
+
+HF_WIDE = os.path.join(os.path.dirname(__file__), "golden", "hf_audio_tower_wide.npz")
+WIDE = {"asr": (synth.EncoderShape("asr-2l", 2, 896, 14, 3584), 21),
+        "aligner": (synth.EncoderShape("aligner-2l", 2, 1024, 16, 4096), 22)}
+
+
+def test_graph_matches_upstream_hf_audio_tower_at_real_widths():
+    """Same pin at the production widths (2-layer towers, d = 896 / 14 heads / ffn 3584 and d = 1024 / 16 heads / ffn 4096,
+    conv 480; make_hf_golden.py WIDE): the restatement in ideal mode reproduces upstream's float64 outputs."""
+    g = np.load(HF_WIDE)
+    filt = np.load(os.path.join(os.path.dirname(GOLD), "mel_ref.npz"))["filters"]
+    erf = EO.Numerics(act_round="none", gelu_table=False, gelu_erf=True, dtype=np.float64)
+    for name, (shape, wseed) in WIDE.items():
+        w = synth.random_weights(shape, wseed)
+        W = EO.Weights({k: v for k, v in synth.stored_weights(w, "f32").items() if "#" not in k}, "f32")
+        kw = dict(n_layers=shape.n_layers, d_model=shape.d_model, n_heads=shape.n_heads)
+        for key in [k for k in g.files if k.startswith(name + ".win_")]:
+            _, seed, n = key.split("_")
+            mel = MO.log_mel_numpy(synth.synth_audio(int(seed), int(n)), filt)
+            win = EO.encode(mel, W, variant="aligner", nm=erf, **kw)
+            assert win.shape == g[key].shape
+            assert np.abs(win - g[key]).max() <= 2e-6 * np.abs(g[key]).max()
+            if mel.shape[1] % 100 == 0:
+                asr = EO.encode(mel, W, variant="asr", nm=erf, **kw)
+                want = g[f"{name}.full_{seed}_{n}"]
+                assert np.abs(asr - want).max() <= 2e-6 * np.abs(want).max()
