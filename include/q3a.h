@@ -199,6 +199,10 @@ int q3a_test_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, f
  * column blocks; cu_seqlens: host int[n_seg+1]. */
 int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
                        int operand_dtype, void* stream);
+/* same with the kernel generation chosen explicitly: 1 = one query tile per CTA (attention.cu), 2 = persistent CTAs with
+ * two ping-ponging query tiles (attention2.cu, what the encoder runs), 0 = the encoder's choice. */
+int q3a_test_attention_v(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
+                         int operand_dtype, int version, void* stream);
 
 /* The library's own bounds check (compute-sanitizer's stand-in where that tool is not available).  With Q3A_GUARD=1
  * in the environment when the process first allocates, every device buffer the library owns (weights, activations,

@@ -67,6 +67,7 @@ SYMBOLS = {
     "q3a_plan_host_call": (_I, [_P, _I, _I, _I, _P, _P, _P]),
     "q3a_test_gemm": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "q3a_test_attention": (_I, [_P, _P, _I, _I, _P, _I, _I, _P]),
+    "q3a_test_attention_v": (_I, [_P, _P, _I, _I, _P, _I, _I, _I, _P]),
     "q3a_debug_check_guards": (_I, [_P, _P]),
     "q3a_debug_damage_guard": (_I, []),
 }
@@ -269,11 +270,12 @@ def test_gemm(a, w, bias, out, operand: int, block_n: int = 0) -> None:
                                out.data_ptr(), M, N, K, operand, block_n, None))
 
 
-def test_attention(qkv, out, n_heads: int, cu_seqlens, operand: int) -> None:
+def test_attention(qkv, out, n_heads: int, cu_seqlens, operand: int, version: int = 0, stream: int = 0) -> None:
+    """version: 0 = what the encoder runs, 1 / 2 = kernel generation (include/q3a.h)"""
     T = qkv.shape[0]
     cu = _int_array(cu_seqlens)
-    check(load().q3a_test_attention(qkv.data_ptr(), out.data_ptr(), T, n_heads, cu, len(cu_seqlens) - 1, operand,
-                                    None))
+    check(load().q3a_test_attention_v(qkv.data_ptr(), out.data_ptr(), T, n_heads, cu, len(cu_seqlens) - 1, operand,
+                                      version, stream or None))
 
 
 def check_guards() -> tuple[int, int]:

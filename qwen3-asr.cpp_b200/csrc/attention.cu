@@ -338,13 +338,7 @@ static int attention_launch_kt(const void* qkv, void* out, int T, int d, const A
     Q3A_TRY(make_tmap_2d(&tm_q, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, 128));
     Q3A_TRY(make_tmap_2d(&tm_kv, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, KT));
     auto kern = attention_kernel<OpT, KT>;
-    static bool attr_set[64] = {false};              // the opt-in is per device
-    int dev = 0;
-    Q3A_CUDA(cudaGetDevice(&dev));
-    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-        Q3A_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmem));
-        if (dev >= 0 && dev < 64) attr_set[dev] = true;
-    }
+    Q3A_TRY(kernel_smem_optin(reinterpret_cast<const void*>(kern), Cfg::kSmem));   // per (kernel, device), thread-safe
     Q3A_CUDA(launch_pdl(kern, dim3(n_tiles, n_heads), dim3(128), Cfg::kSmem, stream, tm_q, tm_kv, tiles_dev, (OpT*)out, d));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
@@ -364,17 +358,25 @@ int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnT
     return attention_launch_kt<__nv_bfloat16, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
 }
 
+int attention_version() {
+    static const int v = getenv("Q3A_ATTN_V1") ? 1 : 2;
+    return v;
+}
+
 }  // namespace q3a
 
-extern "C" int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
-                                  int operand_dtype, void* stream) {
+extern "C" int q3a_test_attention_v(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
+                                    int operand_dtype, int version, void* stream) {
     using namespace q3a;
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device"); return Q3A_ERR_CUDA; }
     Q3A_TRY(use_device(dev));
     if (!qkv_dev || !out_dev || !cu_seqlens || n_seg < 0 || H <= 0) { set_error("test_attention: bad argument"); return Q3A_ERR_ARG; }
+    if (version == 0) version = attention_version();
+    if (version != 1 && version != 2) { set_error("test_attention: version must be 0 (default), 1 or 2"); return Q3A_ERR_ARG; }
     std::vector<AttnTile> tiles;
-    attention_tiles(cu_seqlens, n_seg, tiles);
+    if (version == 1) attention_tiles(cu_seqlens, n_seg, tiles);
+    else attention2_items(cu_seqlens, n_seg, tiles);
     if (tiles.empty()) return Q3A_OK;
     static DevBuf d_tiles_buf;                       // test-only entry point: grow-only scratch, never freed
     Q3A_TRY(d_tiles_buf.reserve(sizeof(AttnTile) * tiles.size()));
@@ -384,7 +386,14 @@ extern "C" int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int
     cudaError_t e = cudaMemcpyAsync(d_tiles, tiles.data(), sizeof(AttnTile) * tiles.size(), cudaMemcpyHostToDevice, st);
     int rc = Q3A_OK;
     if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = Q3A_ERR_CUDA; }
-    if (rc == Q3A_OK) rc = attention_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, st);
+    if (rc == Q3A_OK)
+        rc = version == 1 ? attention_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, st)
+                          : attention2_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, st);
     if (!st) cudaStreamSynchronize(st);               // with a caller's stream the call stays asynchronous
     return rc;
+}
+
+extern "C" int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
+                                  int operand_dtype, void* stream) {
+    return q3a_test_attention_v(qkv_dev, out_dev, T, H, cu_seqlens, n_seg, operand_dtype, 0, stream);
 }

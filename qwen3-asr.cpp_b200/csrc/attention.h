@@ -5,10 +5,10 @@
 namespace q3a {
 
 struct AttnTile {
-    int q0;          // first token row of this 128-query tile
+    int q0;          // first token row of this query tile (v1: 128 rows) / work item (v2: up to 256 rows)
     int seg_start;   // tokens [seg_start, seg_end) attend to each other
     int seg_end;
-    int pad;
+    int pad;         // v2: query rows of the item (1..256); v1: unused
 };
 
 // one tile per 128 queries of every segment; cu_seqlens has n_seg+1 ascending entries
@@ -19,5 +19,14 @@ double attention_flops(const int* cu_seqlens, int n_seg, int n_heads);
 // qkv: [T][3*H*64] 16-bit (q | k | v column blocks), out: [T][H*64] 16-bit
 int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnTile* tiles_dev, int n_tiles, int fmt,
                      cudaStream_t stream);
+
+// ---- second-generation kernel (attention2.cu): persistent CTAs, two query tiles per CTA -------------------------------
+// work items: ceil(len/256) per segment, equal row counts rounded up to whole warps
+void attention2_items(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& items);
+int attention2_item_count(int seg_len);
+int attention2_launch(const void* qkv, void* out, int T, int n_heads, const AttnTile* items_dev, int n_items, int fmt,
+                      cudaStream_t stream);
+// which kernel the encoder uses: 2 unless Q3A_ATTN_V1 is set in the environment (A/B runs)
+int attention_version();
 
 }  // namespace q3a

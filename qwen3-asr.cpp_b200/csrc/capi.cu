@@ -36,6 +36,33 @@ int use_device(int device) {
     return Q3A_OK;
 }
 
+int kernel_smem_optin(const void* kernel, int bytes) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, int>, int> done;      // (kernel, device) -> bytes opted in
+    int dev = 0;
+    Q3A_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = done.find({kernel, dev});
+    if (it != done.end() && it->second >= bytes) return Q3A_OK;
+    Q3A_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done[{kernel, dev}] = bytes;
+    return Q3A_OK;
+}
+
+int sm_count_cached() {
+    static std::mutex mu;
+    static std::map<int, int> cache;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { cudaGetLastError(); return 148; }
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(dev);
+    if (it != cache.end()) return it->second;
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 148; }
+    cache[dev] = n;
+    return n;
+}
+
 // ---- Q3A_GUARD: guard bands around every DevBuf allocation (see common.cuh) ------------------------------
 static std::mutex g_guard_mu;
 static std::map<void*, size_t> g_guards;            // cudaMalloc base -> user bytes between the bands

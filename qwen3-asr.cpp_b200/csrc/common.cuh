@@ -186,6 +186,11 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 
 // make `device` current and check that it is an sm_100 part (there is no other code path)
 int use_device(int device);
+// opt a kernel in to `bytes` of dynamic shared memory, once per (kernel, current device); thread-safe (several encoders
+// on several devices may launch from their own host threads)
+int kernel_smem_optin(const void* kernel, int bytes);
+// multiprocessor count of the current device (cached per device)
+int sm_count_cached();
 
 // counts our kernel launches (reported through q3a_timings::total_launches)
 extern thread_local int g_launch_counter;

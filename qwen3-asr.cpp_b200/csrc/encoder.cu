@@ -215,9 +215,13 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     const int n_seg = (int)cu.size() - 1;
     std::vector<AttnTile> tiles;
     std::vector<int> seg_tile0(n_seg + 1, 0);             // first attention tile of every segment
+    const int attn_v = attention_version();
     if (mode != Q3A_MODE_CONV_ONLY) {
-        attention_tiles(cu.data(), n_seg, tiles);
-        for (int sgi = 0; sgi < n_seg; ++sgi) seg_tile0[sgi + 1] = seg_tile0[sgi] + attention_tile_count(cu[sgi + 1] - cu[sgi]);
+        if (attn_v == 1) attention_tiles(cu.data(), n_seg, tiles); else attention2_items(cu.data(), n_seg, tiles);
+        for (int sgi = 0; sgi < n_seg; ++sgi) {
+            const int len = cu[sgi + 1] - cu[sgi];
+            seg_tile0[sgi + 1] = seg_tile0[sgi] + (attn_v == 1 ? attention_tile_count(len) : attention2_item_count(len));
+        }
     }
 
     const int maxL1 = (max_len - 1) / 2 + 1;
@@ -384,7 +388,8 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
             Q3A_TRY(linear(EPI_BIAS_OP, hr, d, L.w_qkv, 3 * d, rows16(e->qkv.p, 3 * (size_t)d, t0), L.b_qkv, nullptr, nullptr, nullptr, tn));
             {
                 const int sp = prof.begin(SP_ATTN);
-                Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
+                if (attn_v == 1) Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
+                else Q3A_TRY(attention2_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
                 prof.end(sp);
                 e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;
             }

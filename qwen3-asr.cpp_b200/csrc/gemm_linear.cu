@@ -9,15 +9,7 @@
 
 namespace q3a {
 
-int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    }
-    return n;
-}
+int sm_count() { return sm_count_cached(); }
 
 int gemm_prepare_impl(const void* kernel, int smem_bytes, int threads, int* max_pairs) {
     static std::mutex mu;

@@ -40,17 +40,22 @@ def _attn_ref(qkv, H, cu):
 
 
 # outputs reach |o| ~ 5: half an ulp of bf16 there is 1.6e-2 from the output rounding alone, P's rounding adds ~1e-2
+@pytest.mark.parametrize("version", [2, 1])
 @pytest.mark.parametrize("opd,tol", [(B.OP_BF16, 3e-2), (B.OP_F16, 4e-3)])
 @pytest.mark.parametrize("H,cu", [
     (2, [0, 128]), (2, [0, 16]), (1, [0, 1]), (3, [0, 100]), (14, [0, 390]), (16, [0, 104, 208, 250]),
-    (2, [0, 1, 130, 400, 1596]), (4, [0, 129, 129, 257]), (14, [0, 1560]), (16, [104 * i for i in range(16)])])
-def test_attention_matches_fp32_softmax(lib, opd, tol, H, cu):
-    """full (one segment per utterance), windowed (104-token segments), ragged and empty segments"""
+    (2, [0, 1, 130, 400, 1596]), (4, [0, 129, 129, 257]), (14, [0, 1560]), (16, [104 * i for i in range(16)]),
+    (3, [0, 256, 513, 770, 1027, 1028]), (2, [0, 7805]), (14, [390 * i for i in range(24)])])
+def test_attention_matches_fp32_softmax(lib, opd, tol, H, cu, version):
+    """full (one segment per utterance), windowed (104-token segments), ragged and empty segments; both kernel
+    generations (2 = persistent CTAs with two ping-ponging query tiles, what the encoder runs; 1 = one tile per CTA).
+    The added shapes hit v2's item boundaries (256 / 257 rows, a one-row tile B), 61 key blocks with many items per
+    CTA, and more (item, head) units than SMs so that every CTA walks several items."""
     torch.manual_seed(len(cu) * 100 + H)
     T = cu[-1]
     qkv = (torch.randn(T, 3 * H * 64, device="cuda") * 1.5).to(DT[opd])
     out = torch.full((T, H * 64), float("nan"), device="cuda").to(DT[opd])
-    B.test_attention(qkv, out, H, cu, opd)
+    B.test_attention(qkv, out, H, cu, opd, version)
     torch.cuda.synchronize()
     want = _attn_ref(qkv, H, cu)
     assert torch.isfinite(out.float()).all()
