@@ -43,6 +43,31 @@ static uint16_t to_op(float v, int fmt) {
     return u;
 }
 
+static float op_to_float(uint16_t u, int fmt) {
+    if (fmt == OP_F16) { __half h; std::memcpy(&h, &u, 2); return __half2float(h); }
+    __nv_bfloat16 b; std::memcpy(&b, &u, 2);
+    return __bfloat162float(b);
+}
+
+// LayerNorm fold at load time (epilogues.cuh): w [N][K] f32 is replaced by gamma o w; returns bias' = bias + beta . w
+// (from the unfolded weights, double accumulation) and the column sums of the folded weights AFTER rounding to the
+// operand type -- the epilogue subtracts mean * colsum from what the tensor cores computed with exactly those values.
+static void fold_layernorm(std::vector<float>& w, int N, int K, const std::vector<float>& gamma, const std::vector<float>& beta,
+                           const std::vector<float>& bias, int fmt, std::vector<float>& bias_out, std::vector<float>& colsum) {
+    bias_out.assign(N, 0.0f); colsum.assign(N, 0.0f);
+    for (int n = 0; n < N; ++n) {
+        double bw = 0.0, sw = 0.0;
+        float* row = w.data() + (size_t)n * K;
+        for (int k = 0; k < K; ++k) {
+            bw += (double)beta[k] * row[k];
+            row[k] *= gamma[k];
+            sw += (double)op_to_float(to_op(row[k], fmt), fmt);
+        }
+        bias_out[n] = (float)((double)bias[n] + bw);
+        colsum[n] = (float)sw;
+    }
+}
+
 // ---- weight arena ----------------------------------------------------------------------------------
 struct ArenaPlan {
     struct Item { const void** slot; std::vector<uint8_t> bytes; };
@@ -282,6 +307,7 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     if (mode != Q3A_MODE_CONV_ONLY) {
         Q3A_TRY(e->x.reserve((size_t)T * d * 4));
         Q3A_TRY(e->h.reserve((size_t)T * d * 2));
+        if (e->ln_fold) Q3A_TRY(e->stats.reserve((size_t)T * ln_partials(d) * sizeof(float2)));
         Q3A_TRY(e->qkv.reserve((size_t)T * 3 * d * 2));
         Q3A_TRY(e->att.reserve((size_t)T * d * 2));
         Q3A_TRY(e->up.reserve((size_t)T * ffn * 2));
@@ -291,12 +317,19 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     const long long ps1 = (long long)e->rcap1 * F2 * C, ps2 = (long long)e->rcap2 * F3 * C;
 
     // ---- stem, part by part ---------------------------------------------------------------------------------
+    // LayerNorm fold (epilogues.cuh): `out16` / `stats` are the 16-bit copy and the statistics partials of the residual
+    // stream for the rows of this launch (producers write them, LNFOLD consumers read `stats` and `colsum`)
+    const bool fold = e->ln_fold;
+    const int n_part = fold ? ln_partials(d) : 0;
     auto linear = [&](EpiKind kind, const void* A, int K, const void* W, int N, void* out, const float* bias,
-                      const float* res, const float* pe_tab, const int* pos_tab, int rows) -> int {
+                      const float* res, const float* pe_tab, const int* pos_tab, int rows, void* out16 = nullptr,
+                      float2* stats = nullptr, const float* colsum = nullptr) -> int {
         if (rows <= 0) return Q3A_OK;
         LinearArgs a;
         a.a = A; a.M = rows; a.K = K; a.lda = K; a.w = W; a.N = N; a.ldw = K; a.out = out; a.ldc = N;
         a.bias = bias; a.res = res; a.pe = pe_tab; a.pos = pos_tab;
+        a.out16 = out16; a.stats = stats; a.n_part = n_part; a.colsum = colsum;
+        a.ln_inv_d = 1.0f / (float)d; a.ln_eps = hp.layer_norm_eps;
         const int sp = prof.begin(SP_GEMM);
         const int rc = gemm_linear(kind, fmt, a, st);
         prof.end(sp);
@@ -350,6 +383,10 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         if (mode == Q3A_MODE_CONV_ONLY)
             Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, nullptr, nullptr, tn));
+        else if (fold)
+            Q3A_TRY(linear(EPI_POSEMB_F32_DUAL, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
+                           nullptr, nullptr, e->pe.as<float>(), d_pos + t0, tn, rows16(e->h.p, d, t0),
+                           e->stats.as<float2>() + (size_t)t0 * n_part));
         else
             Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, e->pe.as<float>(), d_pos + t0, tn));
@@ -382,25 +419,42 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
             prof.end(sp);
             return rc;
         };
+        float2* str = fold ? e->stats.as<float2>() + (size_t)t0 * n_part : nullptr;
+        auto attention = [&]() -> int {
+            const int sp = prof.begin(SP_ATTN);
+            if (attn_v == 1) Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
+            else Q3A_TRY(attention2_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
+            prof.end(sp);
+            e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;
+            return Q3A_OK;
+        };
+        void* qkvr = rows16(e->qkv.p, 3 * (size_t)d, t0);
         for (int li = l0; li < l1; ++li) {
             const auto& L = e->layers[li];
-            Q3A_TRY(ln(L.ln1_g, L.ln1_b));
-            Q3A_TRY(linear(EPI_BIAS_OP, hr, d, L.w_qkv, 3 * d, rows16(e->qkv.p, 3 * (size_t)d, t0), L.b_qkv, nullptr, nullptr, nullptr, tn));
-            {
-                const int sp = prof.begin(SP_ATTN);
-                if (attn_v == 1) Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
-                else Q3A_TRY(attention2_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
-                prof.end(sp);
-                e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;
+            if (fold) {
+                // h holds the residual stream rounded to 16 bits, `stats` its row sums: no LayerNorm kernel
+                Q3A_TRY(linear(EPI_LNFOLD_OP, hr, d, L.w_qkv, 3 * d, qkvr, L.b_qkv, nullptr, nullptr, nullptr, tn, nullptr, str, L.s_qkv));
+                Q3A_TRY(attention());
+                Q3A_TRY(linear(EPI_BIAS_RES_F32_DUAL, attr, d, L.w_o, d, xr, L.b_o, xr, nullptr, nullptr, tn, hr, str));
+                Q3A_TRY(linear(EPI_LNFOLD_GELU_OP, hr, d, L.w_up, ffn, upr, L.b_up, nullptr, nullptr, nullptr, tn, nullptr, str, L.s_up));
+                Q3A_TRY(linear(EPI_BIAS_RES_F32_DUAL, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn, hr, str));
+                continue;
             }
+            Q3A_TRY(ln(L.ln1_g, L.ln1_b));
+            Q3A_TRY(linear(EPI_BIAS_OP, hr, d, L.w_qkv, 3 * d, qkvr, L.b_qkv, nullptr, nullptr, nullptr, tn));
+            Q3A_TRY(attention());
             Q3A_TRY(linear(EPI_BIAS_RES_F32, attr, d, L.w_o, d, xr, L.b_o, xr, nullptr, nullptr, tn));
             Q3A_TRY(ln(L.ln2_g, L.ln2_b));
             Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, L.w_up, ffn, upr, L.b_up, nullptr, nullptr, nullptr, tn));
             Q3A_TRY(linear(EPI_BIAS_RES_F32, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn));
         }
         if (post) {
-            Q3A_TRY(ln(e->lnp_g, e->lnp_b));
-            Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, e->w_p1, d, attr, e->b_p1, nullptr, nullptr, nullptr, tn));
+            if (fold) {
+                Q3A_TRY(linear(EPI_LNFOLD_GELU_OP, hr, d, e->w_p1, d, attr, e->b_p1, nullptr, nullptr, nullptr, tn, nullptr, str, e->s_p1));
+            } else {
+                Q3A_TRY(ln(e->lnp_g, e->lnp_b));
+                Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, e->w_p1, d, attr, e->b_p1, nullptr, nullptr, nullptr, tn));
+            }
             Q3A_TRY(linear(EPI_BIAS_F32, attr, d, e->w_p2, hp.out_dim, out_dev + (size_t)t0 * hp.out_dim, e->b_p2, nullptr, nullptr,
                            nullptr, tn));
         }
@@ -521,29 +575,46 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
     for (int l = 0; l < hp.n_encoder_layers; ++l) {
         auto& L = e->layers[l];
         const std::string B = "blk." + std::to_string(l) + ".";
-        FETCH(B + "attn_norm.weight", v, d); plan.add_f32(&L.ln1_g, v);
-        FETCH(B + "attn_norm.bias", v, d);   plan.add_f32(&L.ln1_b, v);
+        std::vector<float> g1, b1, g2, b2, bias, bias2, cs;
+        FETCH(B + "attn_norm.weight", g1, d); plan.add_f32(&L.ln1_g, g1);
+        FETCH(B + "attn_norm.bias", b1, d);   plan.add_f32(&L.ln1_b, b1);
         FETCH(B + "attn_q.weight", v, (int64_t)d * d);
         FETCH(B + "attn_k.weight", v2, (int64_t)d * d);
         FETCH(B + "attn_v.weight", v3, (int64_t)d * d);
         packed = v; packed.insert(packed.end(), v2.begin(), v2.end()); packed.insert(packed.end(), v3.begin(), v3.end());
-        plan.add_op(&L.w_qkv, packed, e->fmt);
         FETCH(B + "attn_q.bias", v, d); FETCH(B + "attn_k.bias", v2, d); FETCH(B + "attn_v.bias", v3, d);
-        packed = v; packed.insert(packed.end(), v2.begin(), v2.end()); packed.insert(packed.end(), v3.begin(), v3.end());
-        plan.add_f32(&L.b_qkv, packed);
+        bias = v; bias.insert(bias.end(), v2.begin(), v2.end()); bias.insert(bias.end(), v3.begin(), v3.end());
+        if (e->ln_fold) {
+            fold_layernorm(packed, 3 * d, d, g1, b1, bias, e->fmt, bias2, cs);
+            plan.add_f32(&L.b_qkv, bias2); plan.add_f32(&L.s_qkv, cs);
+        } else plan.add_f32(&L.b_qkv, bias);
+        plan.add_op(&L.w_qkv, packed, e->fmt);
         FETCH(B + "attn_out.weight", v, (int64_t)d * d); plan.add_op(&L.w_o, v, e->fmt);
         FETCH(B + "attn_out.bias", v, d);                plan.add_f32(&L.b_o, v);
-        FETCH(B + "ffn_norm.weight", v, d); plan.add_f32(&L.ln2_g, v);
-        FETCH(B + "ffn_norm.bias", v, d);   plan.add_f32(&L.ln2_b, v);
-        FETCH(B + "ffn_up.weight", v, (int64_t)ffn * d);   plan.add_op(&L.w_up, v, e->fmt);
-        FETCH(B + "ffn_up.bias", v, ffn);                  plan.add_f32(&L.b_up, v);
+        FETCH(B + "ffn_norm.weight", g2, d); plan.add_f32(&L.ln2_g, g2);
+        FETCH(B + "ffn_norm.bias", b2, d);   plan.add_f32(&L.ln2_b, b2);
+        FETCH(B + "ffn_up.weight", v, (int64_t)ffn * d);
+        FETCH(B + "ffn_up.bias", bias, ffn);
+        if (e->ln_fold) {
+            fold_layernorm(v, ffn, d, g2, b2, bias, e->fmt, bias2, cs);
+            plan.add_f32(&L.b_up, bias2); plan.add_f32(&L.s_up, cs);
+        } else plan.add_f32(&L.b_up, bias);
+        plan.add_op(&L.w_up, v, e->fmt);
         FETCH(B + "ffn_down.weight", v, (int64_t)d * ffn); plan.add_op(&L.w_down, v, e->fmt);
         FETCH(B + "ffn_down.bias", v, d);                  plan.add_f32(&L.b_down, v);
     }
-    FETCH("ln_post.weight", v, d); plan.add_f32(&e->lnp_g, v);
-    FETCH("ln_post.bias", v, d);   plan.add_f32(&e->lnp_b, v);
-    FETCH("proj1.weight", v, (int64_t)d * d);           plan.add_op(&e->w_p1, v, e->fmt);
-    FETCH("proj1.bias", v, d);                          plan.add_f32(&e->b_p1, v);
+    {
+        std::vector<float> gp, bp, bias, bias2, cs;
+        FETCH("ln_post.weight", gp, d); plan.add_f32(&e->lnp_g, gp);
+        FETCH("ln_post.bias", bp, d);   plan.add_f32(&e->lnp_b, bp);
+        FETCH("proj1.weight", v, (int64_t)d * d);
+        FETCH("proj1.bias", bias, d);
+        if (e->ln_fold) {
+            fold_layernorm(v, d, d, gp, bp, bias, e->fmt, bias2, cs);
+            plan.add_f32(&e->b_p1, bias2); plan.add_f32(&e->s_p1, cs);
+        } else plan.add_f32(&e->b_p1, bias);
+        plan.add_op(&e->w_p1, v, e->fmt);
+    }
     FETCH("proj2.weight", v, (int64_t)hp.out_dim * d);  plan.add_op(&e->w_p2, v, e->fmt);
     FETCH("proj2.bias", v, hp.out_dim);                 plan.add_f32(&e->b_p2, v);
 #undef FETCH
@@ -576,7 +647,7 @@ extern "C" void q3a_encoder_free(q3a_encoder* e) {
     if (e->stream) cudaStreamSynchronize(e->stream);
     e->arena.release(); e->pe.release();
     e->planes1.release(); e->planes2.release(); e->feat.release(); e->x.release(); e->h.release(); e->qkv.release();
-    e->att.release(); e->up.release(); e->tables.release(); e->stage_in.release(); e->stage_out.release();
+    e->att.release(); e->up.release(); e->stats.release(); e->tables.release(); e->stage_in.release(); e->stage_out.release();
     e->stage_in2.release(); e->stage_out2.release(); e->stage_pcm.release();
     e->stage_mel.release(); e->stage_max.release();
     e->ring.release();
@@ -608,6 +679,7 @@ extern "C" int q3a_encoder_load(const char* gguf_path, int device, int operand_d
     Q3A_TRY(use_device(device));
     q3a_encoder* e = new q3a_encoder();
     e->device = device; e->fmt = operand_dtype;
+    e->ln_fold = getenv("Q3A_NO_LN_FOLD") == nullptr;       // A/B switch: separate layernorm_kernel launches instead
     int rc = load_weights(e, f);
     if (rc == Q3A_OK) {
         bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&
@@ -653,7 +725,7 @@ extern "C" int q3a_encoder_get_timings(const q3a_encoder* e, q3a_timings* out) {
 extern "C" int64_t q3a_encoder_device_bytes(const q3a_encoder* e) {
     if (!e) return 0;
     return (int64_t)(e->arena.cap + e->pe.cap + e->planes1.cap + e->planes2.cap + e->feat.cap + e->x.cap + e->h.cap +
-                     e->qkv.cap + e->att.cap + e->up.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap + e->stage_in2.cap + e->stage_out2.cap + e->stage_pcm.cap +
+                     e->qkv.cap + e->att.cap + e->up.cap + e->stats.cap + e->tables.cap + e->stage_in.cap + e->stage_out.cap + e->stage_in2.cap + e->stage_out2.cap + e->stage_pcm.cap +
                      e->stage_mel.cap + e->stage_max.cap);
 }
 

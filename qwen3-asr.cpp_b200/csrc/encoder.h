@@ -28,15 +28,20 @@ struct q3a_encoder {
     struct Layer {
         const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_o, *b_up, *b_down;
         const void *w_qkv, *w_o, *w_up, *w_down;
+        // LayerNorm fold (ln_fold): w_qkv / w_up hold gamma o W, b_qkv / b_up hold b + beta . W, s_* the column sums of
+        // the folded, rounded weights (epilogues.cuh)
+        const float *s_qkv = nullptr, *s_up = nullptr;
     };
     std::vector<Layer> layers;
     const float *lnp_g = nullptr, *lnp_b = nullptr, *b_p1 = nullptr, *b_p2 = nullptr;
     const void *w_p1 = nullptr, *w_p2 = nullptr;
+    const float* s_p1 = nullptr;
+    bool ln_fold = false;            // LayerNorm folded into the QKV / FFN-up / proj1 GEMMs (no layernorm_kernel launches)
     q3a::DevBuf pe;                  // sinusoidal table [pe_rows][d_model] f32
     int pe_rows = 0;
 
     // ---- workspace (grows, never shrinks) -----------------------------------------------------
-    q3a::DevBuf planes1, planes2, feat, x, h, qkv, att, up, tables, stage_in, stage_out, stage_in2, stage_out2, stage_pcm, stage_mel, stage_max;
+    q3a::DevBuf planes1, planes2, feat, x, h, qkv, att, up, stats, tables, stage_in, stage_out, stage_in2, stage_out2, stage_pcm, stage_mel, stage_max;
     int rcap1 = 0, rcap2 = 0, sigP2 = 0, sigP3 = 0, sigP2_planes2 = 0;   // plane layout the zero rows were prepared for
     q3a::PinnedRing ring;
 

@@ -2,6 +2,7 @@
 // fp32 accumulator columns at a time (see the two contracts in gemm_tc.cuh).
 #pragma once
 #include "common.cuh"
+#include "gemm_tc.cuh"
 
 namespace q3a {
 
@@ -84,6 +85,99 @@ struct EpiPosEmbF32 {
                 load8(prow + g * 8, p);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) v[g * 8 + j] += p[j];
+            }
+        }
+    }
+};
+
+// ---- LayerNorm folded into the GEMMs (audio_encoder.cpp:441-448,502-508,530-534 without a LayerNorm kernel) -----------
+// h = LN(x) * gamma + beta feeds a weight matmul y = h W^T + b.  With W' = gamma o W (folded at load), s[n] = sum_k W'[n][k]
+// and c[n] = b[n] + sum_k beta[k] W[n][k]:      y[m][n] = rstd[m] * (sum_k x[m][k] W'[n][k] - mean[m] * s[n]) + c[n],
+// so the A operand is the residual stream itself rounded to 16 bits and the statistics enter in the epilogue.  The
+// producer of x (conv_out, out-projection, FFN-down) emits that 16-bit copy and per-row partial (sum, sum of squares)
+// next to the f32 stream ("dual" epilogues); partials are added here in a fixed order, so results stay bit-identical
+// whatever the batch around a row looks like.
+//
+// producer side: f32 out = acc + bias (+ out), plus the 16-bit copy and the partials (kernel: EpiDual)
+template <class OpT, bool kRes>
+struct EpiBiasF32Dual {
+    static constexpr bool kStaged = true, kResidual = kRes;
+    static constexpr int kOutBytes = 4;
+    const float* bias;
+    float2* stats; int n_part;
+    __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
+        if (!bias) return;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float b[8];
+                load8(bias + n0 + g * 8, b);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] += b[j];
+            }
+        }
+    }
+};
+template <class OpT>
+struct EpiPosEmbF32Dual {
+    static constexpr bool kStaged = true, kResidual = false;
+    static constexpr int kOutBytes = 4;
+    const float* pe; const int* pos; int ld; int M;
+    float2* stats; int n_part;
+    __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
+    __device__ __forceinline__ void apply(int m, int n0, int nvalid, float (&v)[32]) const {
+        if (!pe || m >= M) return;
+        const float* prow = pe + (size_t)__ldg(pos + m) * ld + n0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float p[8];
+                load8(prow + g * 8, p);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] += p[j];
+            }
+        }
+    }
+};
+template <class OpT, bool kRes> struct EpiDual<EpiBiasF32Dual<OpT, kRes>> { static constexpr bool value = true; };
+template <class OpT> struct EpiDual<EpiPosEmbF32Dual<OpT>> { static constexpr bool value = true; };
+
+// consumer side: 16-bit out = act(rstd * (acc - mean * s[n]) + c[n])
+struct LnRowState { float mean, rstd; };
+template <class OpT, bool kGelu>
+struct EpiLnFoldActOp {
+    static constexpr bool kStaged = true, kResidual = false;
+    static constexpr int kOutBytes = 2;
+    using RowState = LnRowState;
+    const float* c;          // [N] bias + beta . W
+    const float* s;          // [N] column sums of the folded (rounded) weights
+    const float2* stats;     // [M][n_part]
+    int n_part, M;
+    float inv_d, eps;
+    __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
+    __device__ __forceinline__ RowState row_state(int m) const {
+        float sum = 0.0f, sq = 0.0f;
+        if (m < M) {
+            const float2* p = stats + (size_t)m * n_part;
+            for (int i = 0; i < n_part; ++i) { const float2 t = __ldg(p + i); sum += t.x; sq += t.y; }
+        }
+        const float mean = sum * inv_d;
+        const float var = fmaxf(sq * inv_d - mean * mean, 0.0f);
+        return RowState{mean, 1.0f / sqrtf(var + eps)};
+    }
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32], const RowState& rs) const {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float cc[8], ss[8];
+                load8(c + n0 + g * 8, cc);
+                load8(s + n0 + g * 8, ss);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float x = fmaf(rs.rstd, fmaf(-rs.mean, ss[j], v[g * 8 + j]), cc[j]);
+                    v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
+                }
             }
         }
     }

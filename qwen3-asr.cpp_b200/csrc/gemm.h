@@ -10,6 +10,12 @@ enum EpiKind : int {
     EPI_BIAS_F32 = 2,       // f32 out = acc + bias
     EPI_BIAS_RES_F32 = 3,   // f32 out = acc + bias + res
     EPI_POSEMB_F32 = 4,     // f32 out = acc + pe[pos[m]]
+    // LayerNorm folded into the GEMMs (epilogues.cuh): producers of the residual stream also emit its 16-bit copy (out16)
+    // and per-row statistics partials (stats), consumers apply mean / rstd in the epilogue
+    EPI_BIAS_RES_F32_DUAL = 5,   // f32 out = acc + bias + res ; out16 ; stats
+    EPI_POSEMB_F32_DUAL = 6,     // f32 out = acc + pe[pos[m]] ; out16 ; stats
+    EPI_LNFOLD_OP = 7,           // 16-bit out = rstd * (acc - mean * colsum) + bias'
+    EPI_LNFOLD_GELU_OP = 8,      // 16-bit out = gelu(...)
 };
 
 struct LinearArgs {
@@ -24,7 +30,15 @@ struct LinearArgs {
     const float* pe = nullptr;
     const int* pos = nullptr;
     int block_n = 0;           // 0 = pick from N
+    // LayerNorm fold
+    void* out16 = nullptr;     // DUAL: [M][ldc] 16-bit copy of out
+    float2* stats = nullptr;   // DUAL: written [M][n_part]; LNFOLD: read
+    int n_part = 0;            // partials per row = 2 * ceil(d_model / BLOCK_N of the producer): ln_partials()
+    const float* colsum = nullptr;   // LNFOLD: [N]
+    float ln_inv_d = 0.0f, ln_eps = 0.0f;
 };
+// statistics partials per row that a DUAL GEMM with N output columns writes
+int ln_partials(int N);
 
 int gemm_linear(EpiKind kind, int fmt, const LinearArgs& a, cudaStream_t stream);
 

@@ -40,6 +40,12 @@ int gemm_prepare_impl(const void* kernel, int smem_bytes, int threads, int* max_
     return Q3A_OK;
 }
 
+int ln_partials(int N) {
+    int bn = pick_block_n(N);
+    if (bn == 240) bn = 128;
+    return 2 * ceil_div(N, bn);
+}
+
 int pick_block_n(int N) {
     if (N % 256 == 0) return 256;
     if (N % 224 == 0) return 224;
@@ -55,13 +61,15 @@ static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t strea
     Q3A_TRY(make_tmap_2d(&ta, a.a, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, kBlockM));
     Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldw, BLOCK_N / 2));
     Q3A_TRY(make_tmap_tile32(&tc_, a.out, Epi::kOutBytes, (uint64_t)a.M, (uint64_t)a.N, (uint64_t)a.ldc));
+    CUtensorMap tc2 = tc_;
+    if (EpiDual<Epi>::value) Q3A_TRY(make_tmap_tile32(&tc2, a.out16, 2, (uint64_t)a.M, (uint64_t)a.N, (uint64_t)a.ldc));
     auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderLinear, Epi>;
     int pairs = 0;
     Q3A_TRY(gemm_prepare(kern, S::kTotal, &pairs));
     LoaderLinear loader{ceil_div(a.K, kBlockK)};
     const int tiles = ceil_div(a.M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
     const int grid = 2 * (tiles < pairs ? tiles : pairs);
-    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, tc_, a.M, a.N, loader, epi));
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, tc_, tc2, a.M, a.N, loader, epi));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;
@@ -82,6 +90,21 @@ static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) 
             return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias}, stream);
         case EPI_POSEMB_F32:
             return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32{a.pe, a.pos, a.ldc, a.M}, stream);
+        case EPI_BIAS_RES_F32_DUAL:
+        case EPI_POSEMB_F32_DUAL:
+            if (!a.out16 || !a.stats || a.n_part != 2 * ceil_div(a.N, BLOCK_N)) {
+                set_error("gemm_linear: dual output needs out16, stats and n_part = ln_partials(N)"); return Q3A_ERR_ARG;
+            }
+            if (kind == EPI_POSEMB_F32_DUAL)
+                return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32Dual<OpT>{a.pe, a.pos, a.ldc, a.M, a.stats, a.n_part}, stream);
+            if (a.res != a.out) { set_error("gemm_linear: the residual must be the output matrix (updated in place)"); return Q3A_ERR_ARG; }
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32Dual<OpT, true>{a.bias, a.stats, a.n_part}, stream);
+        case EPI_LNFOLD_OP:
+        case EPI_LNFOLD_GELU_OP:
+            if (!a.bias || !a.colsum || !a.stats || a.n_part <= 0) { set_error("gemm_linear: LayerNorm fold needs bias', colsum and stats"); return Q3A_ERR_ARG; }
+            if (kind == EPI_LNFOLD_OP)
+                return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldActOp<OpT, false>{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldActOp<OpT, true>{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps}, stream);
     }
     set_error("gemm_linear: unknown epilogue");
     return Q3A_ERR_ARG;

@@ -26,6 +26,8 @@
 #include "common.cuh"
 #include "tc.cuh"
 
+#include <type_traits>
+
 namespace q3a {
 
 constexpr int kBlockM = 128;                // rows per CTA; a pair covers 256
@@ -36,7 +38,8 @@ constexpr int kEpiWarps = 8;
 constexpr int kTmemCols = 512;              // two accumulator buffers of up to 256 columns
 constexpr int kSmemLimit = 232448;          // 227 KB opt-in maximum per CTA
 
-// kEpiBufBytes: bytes of one epilogue staging buffer (32 rows), kEpiBufs: buffers per epilogue warp
+// kEpiBufBytes: bytes of one epilogue staging buffer set (32 rows; a dual-output epilogue stages the f32 chunk and its
+// 16-bit copy), kEpiBufs: buffer sets per epilogue warp
 template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs> struct GemmSmem {
     static constexpr int kABytes = kBlockM * kBlockK * 2;              // 16 KB
     static constexpr int kBBytes = (BLOCK_N / 2) * kBlockK * 2;        // this CTA's half of the W tile
@@ -50,9 +53,14 @@ template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs> struct GemmSmem {
     static_assert(kStages >= 3, "need at least three stages");
 };
 // the shared-memory plan of a (BLOCK_N, epilogue) instantiation, for kernel and host alike
+template <class Epi> struct EpiDual { static constexpr bool value = false; };     // specialised by dual-output epilogues
 template <int BLOCK_N, class Epi>
-using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes : 0,
-                             Epi::kStaged ? (Epi::kResidual ? 3 : 2) : 0>;
+using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes + (EpiDual<Epi>::value ? 32 * 32 * 2 : 0) : 0,
+                             Epi::kStaged ? (Epi::kResidual && !EpiDual<Epi>::value ? 3 : 2) : 0>;
+// per-row state an epilogue may carry across the column chunks of a tile (LayerNorm-folded epilogues keep mean / rstd)
+struct NoRowState {};
+template <class Epi, class = void> struct EpiRowState { using type = NoRowState; };
+template <class Epi> struct EpiRowState<Epi, decltype((void)sizeof(typename Epi::RowState))> { using type = typename Epi::RowState; };
 
 // ---- A-operand coordinate policies (m128 = index of this CTA's 128-row block) -----------------
 // The producer and the MMA issuer walk the K blocks of a tile with a small iterator that is advanced
@@ -111,19 +119,32 @@ __device__ __forceinline__ uint32_t stage_off(int r, int j) {
 //                       __device__ void apply(int m, int n0, int nvalid, float (&v)[32]) const; }
 //            v holds the accumulators of row m, columns n0..n0+31 on entry and the values to store on
 //            exit (the kernel adds the residual afterwards); tmap_c describes the output matrix.
+//            Optional: `using RowState = ...; RowState row_state(int m) const;` -> apply(m, n0, nvalid, v, rs) gets it
+//            (loaded once per tile, e.g. the row's LayerNorm statistics).
+//            Optional dual output (EpiDual<E>::value, f32 epilogues only): the final f32 chunk is also stored as 16-bit
+//            operand type through tmap_c2, and per-row (sum, sum of squares) partials of the final values go to
+//            epi.stats[m * epi.n_part + n_blk * 2 + half] -- the next GEMM folds the LayerNorm in (epilogues.cuh).
 //   direct   struct E { static constexpr bool kStaged = false;
 //                       __device__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const; }
 //            called for rows m < M; only the first nvalid (multiple of 8) columns belong to the output.
 template <int BLOCK_N, int kFmt, class Loader, class Epilogue>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-               const __grid_constant__ CUtensorMap tmap_c, int M, int N, Loader loader, Epilogue epi) {
+               const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c2, int M, int N,
+               Loader loader, Epilogue epi) {
     constexpr bool kStaged = Epilogue::kStaged;
     constexpr bool kResidual = Epilogue::kResidual;
+    constexpr bool kDual = EpiDual<Epilogue>::value;
     constexpr int kOutBytes = Epilogue::kOutBytes;                     // 4 or 2 (staged only)
     constexpr int kRowBytes = 32 * kOutBytes;                          // staging row: 32 columns
-    constexpr int kBufBytes = kStaged ? 32 * kRowBytes : 0;
-    constexpr int kEpiBufs = kStaged ? (kResidual ? 3 : 2) : 0;
+    constexpr int kMainBytes = kStaged ? 32 * kRowBytes : 0;           // the chunk in the output type
+    constexpr int kBufBytes = kMainBytes + (kDual ? 32 * 64 : 0);      // + its 16-bit copy (64-byte rows)
+    static_assert(!kDual || (kStaged && kOutBytes == 4), "dual output: staged f32 epilogues only");
+    // Buffer sets per epilogue warp.  Residual epilogues rotate three (next chunk's residual landing | current chunk |
+    // previous chunk being stored); the dual-output ones make do with two 6-KB sets -- the prefetch of chunk i+1 then
+    // waits for the store of chunk i-1 to have READ its buffer (lane 0 only, ~100 clk, under the other lanes' tcgen05.ld) --
+    // so that the stage ring keeps its depth.
+    constexpr int kEpiBufs = kStaged ? (kResidual && !kDual ? 3 : 2) : 0;
     using S = GemmSmemFor<BLOCK_N, Epilogue>;
     constexpr int kStages = S::kStages;
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "BLOCK_N must be a multiple of 16, at most 256");
@@ -157,6 +178,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         tc::prefetch_tmap(&tmap_a);
         tc::prefetch_tmap(&tmap_b);
         if (kStaged) tc::prefetch_tmap(&tmap_c);
+        if (kDual) tc::prefetch_tmap(&tmap_c2);
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), 1); }
@@ -252,8 +274,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // residual prefetch for the chunk with sequence number sq at (tile, chunk c)
         auto issue_res = [&](uint32_t sq, int tile, int c) {
             const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
-            const int b = sq % 3;
-            tc::mbar_arrive_expect_tx(res_bar(ew, b), kBufBytes);
+            const int b = sq % kEpiBufs;
+            tc::mbar_arrive_expect_tx(res_bar(ew, b), kMainBytes);
             tc::tma_load_2d(my_bufs + b * kBufBytes, &tmap_c, res_bar(ew, b), n_blk * BLOCK_N + c * 32,
                             (2 * m_blk + (int)rank) * kBlockM + q * 32);
         };
@@ -277,19 +299,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int m0 = (2 * m_blk + (int)rank) * kBlockM + q * 32;
             const int m = m0 + lane;
             const uint32_t t_row = tmem_base + as * 256 + ((uint32_t)(q * 32) << 16);
+            typename EpiRowState<Epilogue>::type rs{};
+            if constexpr (!std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value) rs = epi.row_state(m);
+            float st_sum = 0.0f, st_sq = 0.0f;             // dual output: this warp's share of the row's statistics
 #pragma unroll 1
             for (int c = hf; c < nch; c += 2) {
                 const int n0 = n_blk * BLOCK_N + c * 32;
                 const int nvalid = min(32, min(BLOCK_N - c * 32, N - n0));
-                if (kResidual && lane == 0) {
-                    // next chunk of this warp: same tile, or the first chunk of its next tile
-                    int nt = tile, nc = c + 2;
-                    if (nc >= nch) { nt = tile_with_chunk(tile + num_pairs); nc = hf; }
-                    if (nt < num_tiles) {
-                        tc::bulk_wait_group_read<1>();          // the store that last used that buffer has read it
-                        issue_res(seq + 1, nt, nc);
+                auto prefetch_next_residual = [&]() {
+                    if (kResidual && lane == 0) {
+                        // next chunk of this warp: same tile, or the first chunk of its next tile
+                        int nt = tile, nc = c + 2;
+                        if (nc >= nch) { nt = tile_with_chunk(tile + num_pairs); nc = hf; }
+                        if (nt < num_tiles) {
+                            tc::bulk_wait_group_read<(kEpiBufs > 2 ? kEpiBufs - 2 : 0)>();   // the store that last used that buffer has read it
+                            issue_res(seq + 1, nt, nc);
+                        }
                     }
-                }
+                };
+                // three buffer sets: the prefetch goes out first.  Two (dual output): it targets the buffer the previous
+                // chunk's store is still reading, so it goes out after the accumulator load and the functor, by which
+                // time that read has long finished and lane 0 does not hold up the warp's aligned tcgen05.ld.
+                if constexpr (kEpiBufs > 2) prefetch_next_residual();
                 uint32_t r[32];
                 tc::tmem_ld_32x32b_x32(t_row + c * 32, r);
                 tc::tmem_ld_wait();
@@ -299,7 +330,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if constexpr (!kStaged) {
                     if (m < M) epi(m, n0, nvalid, v);
                 } else {
-                    epi.apply(m, n0, nvalid, v);
+                    if constexpr (std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value) epi.apply(m, n0, nvalid, v);
+                    else epi.apply(m, n0, nvalid, v, rs);
+                    if constexpr (kEpiBufs <= 2) prefetch_next_residual();
                     const int b = seq % kEpiBufs;
                     uint8_t* buf = my_bufs_gen + b * kBufBytes;
                     if constexpr (kResidual) {
@@ -311,6 +344,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             float4 x = *p;
                             x.x += v[4 * j + 0]; x.y += v[4 * j + 1]; x.z += v[4 * j + 2]; x.w += v[4 * j + 3];
                             *p = x;
+                            if constexpr (kDual) { v[4 * j + 0] = x.x; v[4 * j + 1] = x.y; v[4 * j + 2] = x.z; v[4 * j + 3] = x.w; }
                         }
                     } else {
                         if (lane == 0) tc::bulk_wait_group_read<kEpiBufs - 1>();   // buffer b's previous store has read it
@@ -332,14 +366,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                             }
                         }
                     }
+                    if constexpr (kDual) {
+                        // v now holds the final f32 values of the chunk: their 16-bit copy is the next GEMM's A operand, their
+                        // sums feed its folded LayerNorm.  Columns past nvalid (a ragged last chunk) do not count.
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            if (j * 8 < nvalid) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) { st_sum += v[8 * j + i]; st_sq = fmaf(v[8 * j + i], v[8 * j + i], st_sq); }
+                            }
+                            uint4 u;
+                            u.x = Epilogue::pack2(v[8 * j + 0], v[8 * j + 1]);
+                            u.y = Epilogue::pack2(v[8 * j + 2], v[8 * j + 3]);
+                            u.z = Epilogue::pack2(v[8 * j + 4], v[8 * j + 5]);
+                            u.w = Epilogue::pack2(v[8 * j + 6], v[8 * j + 7]);
+                            *reinterpret_cast<uint4*>(buf + kMainBytes + stage_off<64>(lane, j)) = u;
+                        }
+                    }
                     tc::fence_proxy_async();          // generic-proxy smem writes -> visible to the TMA store
                     __syncwarp();
                     if (lane == 0) {
                         tc::tma_store_2d(&tmap_c, my_bufs + b * kBufBytes, n0, m0);
+                        if constexpr (kDual) tc::tma_store_2d(&tmap_c2, my_bufs + b * kBufBytes + kMainBytes, n0, m0);
                         tc::bulk_commit_group();
                     }
                     ++seq;
                 }
+            }
+            if constexpr (kDual) {
+                // one (sum, sum of squares) partial per (row, column block, warp half), always written (zeros when this
+                // warp owned no chunk of the tile) so that the consumer can add all of them in a fixed order
+                if (m < M) epi.stats[(size_t)m * epi.n_part + n_blk * 2 + hf] = make_float2(st_sum, st_sq);
             }
             // every tcgen05.ld of this tile has completed: hand the accumulator buffer back to the MMA issuer
             tc::fence_before_sync();

@@ -1,12 +1,32 @@
 #!/bin/bash
-# round 2, visit A: attention v2 bring-up, the new parity tests, a bench line
+# round 2, visit A: attention v2 + LayerNorm-fold bring-up, the new parity tests, A/B bench lines
 set -u
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests/test_gemm_attention_gpu.py -x -q -m gpu -k attention > gpurun_out/r2a_attn_pytest.log 2>&1
 rc=$?; echo "attention pytest exit=$rc" | tee -a gpurun_out/r2a_attn_pytest.log
 tail -5 gpurun_out/r2a_attn_pytest.log
 if [ $rc -ne 0 ]; then export Q3A_ATTN_V1=1; export ATTN_V=1; echo "FALLING BACK TO ATTENTION V1 FOR THE REST"; fi
-timeout 300 python scripts/gpu_attn_bench.py > gpurun_out/r2a_attn_bench.log 2>&1; echo "attn bench exit=$?"; cat gpurun_out/r2a_attn_bench.log | tail -12
-timeout 1500 python -m pytest tests/test_encoder_gpu.py -x -q -m gpu -s -k "real_widths or device_entry or pad_rows or full_shape or three_way or tiny_q8 or 30s_clip" > gpurun_out/r2a_pytest.log 2>&1; echo "pytest exit=$?" | tee -a gpurun_out/r2a_pytest.log
+timeout 300 python scripts/gpu_attn_bench.py > gpurun_out/r2a_attn_bench.log 2>&1; echo "attn bench exit=$?"; tail -12 gpurun_out/r2a_attn_bench.log
+timeout 900 python -m pytest tests/test_encoder_gpu.py -x -q -m gpu -k "tiny_tower or hf_audio_tower or debug_variants or golden" > gpurun_out/r2a_fold_pytest.log 2>&1
+rc=$?; echo "fold pytest exit=$rc" | tee -a gpurun_out/r2a_fold_pytest.log; tail -5 gpurun_out/r2a_fold_pytest.log
+if [ $rc -ne 0 ]; then
+  Q3A_NO_LN_FOLD=1 timeout 900 python -m pytest tests/test_encoder_gpu.py -x -q -m gpu -k "tiny_tower or hf_audio_tower or debug_variants or golden" > gpurun_out/r2a_nofold_pytest.log 2>&1
+  echo "nofold pytest exit=$?" | tee -a gpurun_out/r2a_nofold_pytest.log; tail -5 gpurun_out/r2a_nofold_pytest.log
+  export Q3A_NO_LN_FOLD=1; echo "FALLING BACK TO UNFUSED LAYERNORM FOR THE REST"
+fi
+timeout 1500 python -m pytest tests/test_encoder_gpu.py -x -q -m gpu -s -k "device_entry or pad_rows or full_shape or three_way or tiny_q8 or 30s_clip or batch_invariance" > gpurun_out/r2a_pytest.log 2>&1; echo "pytest exit=$?" | tee -a gpurun_out/r2a_pytest.log
+tail -12 gpurun_out/r2a_pytest.log
 timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/r2a_bench.json 2> gpurun_out/r2a_bench.err; echo "bench exit=$?"
-tail -15 gpurun_out/r2a_pytest.log; cat gpurun_out/r2a_bench.json; tail -3 gpurun_out/r2a_bench.err
+cat gpurun_out/r2a_bench.json; tail -3 gpurun_out/r2a_bench.err
+Q3A_NO_LN_FOLD=1 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r2a_bench_nofold.json 2> gpurun_out/r2a_bench_nofold.err; echo "bench nofold exit=$?"
+Q3A_ATTN_V1=1 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r2a_bench_attnv1.json 2> gpurun_out/r2a_bench_attnv1.err; echo "bench attn v1 exit=$?"
+python - <<'PY'
+import json
+for n in ("r2a_bench", "r2a_bench_nofold", "r2a_bench_attnv1"):
+    try:
+        d = json.load(open(f"gpurun_out/{n}.json"))
+        print(n, "ms/step", round(d["ms_per_step"], 3), "value", round(d["value"]), "e2e", round(d["e2e"]["value"]), "gemm frac", round(d["roofline"]["frac"], 3),
+              "attn frac", round(d["roofline_attention"]["frac"], 3), "attn ms", round(d["roofline_attention"]["ms_per_step"], 3), "launches", d["gpu_launches"])
+    except Exception as ex:
+        print(n, "unreadable", ex)
+PY
