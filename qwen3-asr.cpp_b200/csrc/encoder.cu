@@ -82,6 +82,11 @@ struct ArenaPlan {
         Item it; it.slot = slot; it.bytes = v;
         items.push_back(std::move(it));
     }
+    void add_bytes(const void** slot, const void* src, size_t n) {
+        Item it; it.slot = slot;
+        it.bytes.assign(static_cast<const uint8_t*>(src), static_cast<const uint8_t*>(src) + n);
+        items.push_back(std::move(it));
+    }
     void add_op(const void** slot, const std::vector<float>& v, int fmt) {
         Item it; it.slot = slot;
         it.bytes.resize(v.size() * 2);
@@ -321,12 +326,12 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     // stream for the rows of this launch (producers write them, LNFOLD consumers read `stats` and `colsum`)
     const bool fold = e->ln_fold;
     const int n_part = fold ? ln_partials(d) : 0;
-    auto linear = [&](EpiKind kind, const void* A, int K, const void* W, int N, void* out, const float* bias,
+    auto linear = [&](EpiKind kind, const void* A, int K, const q3a_encoder::Wt& W, int N, void* out, const float* bias,
                       const float* res, const float* pe_tab, const int* pos_tab, int rows, void* out16 = nullptr,
                       float2* stats = nullptr, const float* colsum = nullptr) -> int {
         if (rows <= 0) return Q3A_OK;
         LinearArgs a;
-        a.a = A; a.M = rows; a.K = K; a.lda = K; a.w = W; a.N = N; a.ldw = K; a.out = out; a.ldc = N;
+        a.a = A; a.M = rows; a.K = K; a.lda = K; a.w = W.p; a.w_d = W.d; a.N = N; a.ldw = K; a.out = out; a.ldc = N;
         a.bias = bias; a.res = res; a.pe = pe_tab; a.pos = pos_tab;
         a.out16 = out16; a.stats = stats; a.n_part = n_part; a.colsum = colsum;
         a.ln_inv_d = 1.0f / (float)d; a.ln_eps = hp.layer_norm_eps;
@@ -381,14 +386,14 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
             e->tm.gemm_flops += 2.0 * (double)tn * F3 * C * 9.0 * C; ++e->tm.gemm_launches;
         }
         if (mode == Q3A_MODE_CONV_ONLY)
-            Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
+            Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, q3a_encoder::Wt{e->conv_out_w, nullptr}, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, nullptr, nullptr, tn));
         else if (fold)
-            Q3A_TRY(linear(EPI_POSEMB_F32_DUAL, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
+            Q3A_TRY(linear(EPI_POSEMB_F32_DUAL, rows16(e->feat.p, feat_dim, t0), feat_dim, q3a_encoder::Wt{e->conv_out_w, nullptr}, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, e->pe.as<float>(), d_pos + t0, tn, rows16(e->h.p, d, t0),
                            e->stats.as<float2>() + (size_t)t0 * n_part));
         else
-            Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, e->conv_out_w, d, stem_out + (size_t)t0 * d,
+            Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, q3a_encoder::Wt{e->conv_out_w, nullptr}, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, e->pe.as<float>(), d_pos + t0, tn));
     }
     prof.end(sp_stem);
@@ -529,6 +534,10 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
     if (hp.n_window_infer != 800) { set_error("only n_window_infer = 800 (104-token attention windows) is supported"); return Q3A_ERR_FORMAT; }
     hp.out_dim = (int)t_p2->ne[1];
     hp.weight_ftype = (int)t_up->type;
+    // Q8_0 files keep their Linear weights quantised on the device unless Q3A_Q8_DEQUANT_AT_LOAD is set; gamma cannot be
+    // folded into 32-element blocks that share one scale, so that path runs the separate LayerNorm kernel
+    e->q8_fused = hp.weight_ftype == (int)GGML_Q8_0 && getenv("Q3A_Q8_DEQUANT_AT_LOAD") == nullptr;
+    if (e->q8_fused) e->ln_fold = false;
     const int d = hp.d_model, C = hp.conv_channels, ffn = hp.ffn_dim, F3 = hp.n_mel_bins / 8;
     if (hp.n_mel_bins != 128) { set_error("only 128 mel bins are supported"); return Q3A_ERR_FORMAT; }
     if (hp.n_attention_heads * 64 != d) { set_error("head_dim must be 64 (d_model = 64 * heads)"); return Q3A_ERR_FORMAT; }
@@ -571,52 +580,78 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
             for (int ff = 0; ff < F3; ++ff) packed[(size_t)n * C * F3 + ff * C + c] = v[(size_t)n * C * F3 + c * F3 + ff];
     plan.add_op(&e->conv_out_w, packed, e->fmt);
 
+    // Linear weights.  16-bit path: dequantised to f32 here, rounded once to the operand type (optionally with the
+    // LayerNorm folded in).  Fused Q8_0 path (Q8_0 file, K % 64 == 0): the ggml blocks go to the device as they are,
+    // de-interleaved into an int8 plane and an f16 scale plane; the GEMM's dequant warps expand them (gemm_tc.cuh).
+    auto q8_ok = [&](const std::string& name) {
+        const GgufTensor* t = f.find(P + name);
+        return e->q8_fused && t && t->type == GGML_Q8_0 && t->ne.size() == 2 && t->ne[0] % 64 == 0;
+    };
+    auto add_linear = [&](q3a_encoder::Wt* slot, const std::vector<std::string>& names, int64_t N_each, int64_t K,
+                          const std::vector<float>* gamma, const std::vector<float>* beta, std::vector<float>* bias,
+                          const float** colsum_slot) -> bool {
+        bool all_q8 = true;
+        for (const auto& nm : names) all_q8 = all_q8 && q8_ok(nm);
+        if (all_q8) {
+            std::vector<int8_t> q, qa; std::vector<uint16_t> dd, da;
+            for (const auto& nm : names) {
+                const GgufTensor* t = f.find(P + nm);
+                if (t->n_elements() != N_each * K) { err = "tensor " + nm + " has an unexpected size"; return false; }
+                if (!f.read_q8_planes(*t, q, dd, err)) return false;
+                qa.insert(qa.end(), q.begin(), q.end()); da.insert(da.end(), dd.begin(), dd.end());
+            }
+            plan.add_bytes(&slot->p, qa.data(), qa.size());
+            plan.add_bytes(&slot->d, da.data(), da.size() * 2);
+            return true;
+        }
+        std::vector<float> w, one;
+        for (const auto& nm : names) {
+            if (!fetch(f, P + nm, one, err, N_each * K)) return false;
+            w.insert(w.end(), one.begin(), one.end());
+        }
+        if (gamma) {
+            std::vector<float> bias2, cs;
+            fold_layernorm(w, (int)(N_each * (int64_t)names.size()), (int)K, *gamma, *beta, *bias, e->fmt, bias2, cs);
+            *bias = bias2;
+            plan.add_f32(colsum_slot, cs);
+        }
+        plan.add_op(&slot->p, w, e->fmt);
+        return true;
+    };
+#define LINEAR(...) do { if (!add_linear(__VA_ARGS__)) { set_error(err); return Q3A_ERR_FORMAT; } } while (0)
+    const bool fold = e->ln_fold;
     e->layers.assign(hp.n_encoder_layers, q3a_encoder::Layer{});
     for (int l = 0; l < hp.n_encoder_layers; ++l) {
         auto& L = e->layers[l];
         const std::string B = "blk." + std::to_string(l) + ".";
-        std::vector<float> g1, b1, g2, b2, bias, bias2, cs;
+        std::vector<float> g1, b1, g2, b2, bias;
         FETCH(B + "attn_norm.weight", g1, d); plan.add_f32(&L.ln1_g, g1);
         FETCH(B + "attn_norm.bias", b1, d);   plan.add_f32(&L.ln1_b, b1);
-        FETCH(B + "attn_q.weight", v, (int64_t)d * d);
-        FETCH(B + "attn_k.weight", v2, (int64_t)d * d);
-        FETCH(B + "attn_v.weight", v3, (int64_t)d * d);
-        packed = v; packed.insert(packed.end(), v2.begin(), v2.end()); packed.insert(packed.end(), v3.begin(), v3.end());
         FETCH(B + "attn_q.bias", v, d); FETCH(B + "attn_k.bias", v2, d); FETCH(B + "attn_v.bias", v3, d);
         bias = v; bias.insert(bias.end(), v2.begin(), v2.end()); bias.insert(bias.end(), v3.begin(), v3.end());
-        if (e->ln_fold) {
-            fold_layernorm(packed, 3 * d, d, g1, b1, bias, e->fmt, bias2, cs);
-            plan.add_f32(&L.b_qkv, bias2); plan.add_f32(&L.s_qkv, cs);
-        } else plan.add_f32(&L.b_qkv, bias);
-        plan.add_op(&L.w_qkv, packed, e->fmt);
-        FETCH(B + "attn_out.weight", v, (int64_t)d * d); plan.add_op(&L.w_o, v, e->fmt);
+        LINEAR(&L.w_qkv, {B + "attn_q.weight", B + "attn_k.weight", B + "attn_v.weight"}, d, d, fold ? &g1 : nullptr, &b1, &bias, &L.s_qkv);
+        plan.add_f32(&L.b_qkv, bias);
+        LINEAR(&L.w_o, {B + "attn_out.weight"}, d, d, nullptr, nullptr, nullptr, nullptr);
         FETCH(B + "attn_out.bias", v, d);                plan.add_f32(&L.b_o, v);
         FETCH(B + "ffn_norm.weight", g2, d); plan.add_f32(&L.ln2_g, g2);
         FETCH(B + "ffn_norm.bias", b2, d);   plan.add_f32(&L.ln2_b, b2);
-        FETCH(B + "ffn_up.weight", v, (int64_t)ffn * d);
         FETCH(B + "ffn_up.bias", bias, ffn);
-        if (e->ln_fold) {
-            fold_layernorm(v, ffn, d, g2, b2, bias, e->fmt, bias2, cs);
-            plan.add_f32(&L.b_up, bias2); plan.add_f32(&L.s_up, cs);
-        } else plan.add_f32(&L.b_up, bias);
-        plan.add_op(&L.w_up, v, e->fmt);
-        FETCH(B + "ffn_down.weight", v, (int64_t)d * ffn); plan.add_op(&L.w_down, v, e->fmt);
+        LINEAR(&L.w_up, {B + "ffn_up.weight"}, ffn, d, fold ? &g2 : nullptr, &b2, &bias, &L.s_up);
+        plan.add_f32(&L.b_up, bias);
+        LINEAR(&L.w_down, {B + "ffn_down.weight"}, d, ffn, nullptr, nullptr, nullptr, nullptr);
         FETCH(B + "ffn_down.bias", v, d);                  plan.add_f32(&L.b_down, v);
     }
     {
-        std::vector<float> gp, bp, bias, bias2, cs;
+        std::vector<float> gp, bp, bias;
         FETCH("ln_post.weight", gp, d); plan.add_f32(&e->lnp_g, gp);
         FETCH("ln_post.bias", bp, d);   plan.add_f32(&e->lnp_b, bp);
-        FETCH("proj1.weight", v, (int64_t)d * d);
         FETCH("proj1.bias", bias, d);
-        if (e->ln_fold) {
-            fold_layernorm(v, d, d, gp, bp, bias, e->fmt, bias2, cs);
-            plan.add_f32(&e->b_p1, bias2); plan.add_f32(&e->s_p1, cs);
-        } else plan.add_f32(&e->b_p1, bias);
-        plan.add_op(&e->w_p1, v, e->fmt);
+        LINEAR(&e->w_p1, {"proj1.weight"}, d, d, fold ? &gp : nullptr, &bp, &bias, &e->s_p1);
+        plan.add_f32(&e->b_p1, bias);
     }
-    FETCH("proj2.weight", v, (int64_t)hp.out_dim * d);  plan.add_op(&e->w_p2, v, e->fmt);
+    LINEAR(&e->w_p2, {"proj2.weight"}, hp.out_dim, d, nullptr, nullptr, nullptr, nullptr);
     FETCH("proj2.bias", v, hp.out_dim);                 plan.add_f32(&e->b_p2, v);
+#undef LINEAR
 #undef FETCH
 
     size_t total = 0;

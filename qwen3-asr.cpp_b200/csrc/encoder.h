@@ -25,16 +25,19 @@ struct q3a_encoder {
     const float *conv1_w = nullptr, *conv1_b = nullptr, *conv2_b = nullptr, *conv3_b = nullptr;
     const void *conv2_w = nullptr, *conv3_w = nullptr, *conv_out_w = nullptr;
     const void* conv1_wimg = nullptr;   // smem image of the conv1 weights for conv1_tc_kernel (null: CUDA-core conv1)
+    // a Linear weight: [N][K] 16-bit operands, or -- Q8_0 file, fused-dequant path -- p = int8 plane, d = f16 block scales
+    struct Wt { const void* p = nullptr; const void* d = nullptr; };
     struct Layer {
         const float *ln1_g, *ln1_b, *ln2_g, *ln2_b, *b_qkv, *b_o, *b_up, *b_down;
-        const void *w_qkv, *w_o, *w_up, *w_down;
+        Wt w_qkv, w_o, w_up, w_down;
         // LayerNorm fold (ln_fold): w_qkv / w_up hold gamma o W, b_qkv / b_up hold b + beta . W, s_* the column sums of
         // the folded, rounded weights (epilogues.cuh)
         const float *s_qkv = nullptr, *s_up = nullptr;
     };
     std::vector<Layer> layers;
     const float *lnp_g = nullptr, *lnp_b = nullptr, *b_p1 = nullptr, *b_p2 = nullptr;
-    const void *w_p1 = nullptr, *w_p2 = nullptr;
+    Wt w_p1, w_p2;
+    bool q8_fused = false;           // Linear weights stay Q8_0 in device memory, dequantised inside the GEMM (gemm_tc.cuh kWq8)
     const float* s_p1 = nullptr;
     bool ln_fold = false;            // LayerNorm folded into the QKV / FFN-up / proj1 GEMMs (no layernorm_kernel launches)
     q3a::DevBuf pe;                  // sinusoidal table [pe_rows][d_model] f32

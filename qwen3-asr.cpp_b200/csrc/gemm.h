@@ -21,7 +21,8 @@ enum EpiKind : int {
 struct LinearArgs {
     const void* a = nullptr;   // [M][K] 16-bit, leading dimension lda
     int M = 0, K = 0, lda = 0;
-    const void* w = nullptr;   // [N][K] 16-bit, leading dimension ldw
+    const void* w = nullptr;   // [N][K] 16-bit, leading dimension ldw; or, with w_d set, the int8 plane of Q8_0 weights
+    const void* w_d = nullptr; // Q8_0 only: [N][K/32] f16 block scales (fused-dequant path, K % 64 == 0)
     int N = 0, ldw = 0;
     void* out = nullptr;       // [M][ldc], 16-bit or f32 depending on the epilogue
     int ldc = 0;

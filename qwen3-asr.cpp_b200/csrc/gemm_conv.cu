@@ -33,7 +33,7 @@ static int launch_conv(const ConvArgs& a, const Epi& epi, cudaStream_t stream) {
     const int M = a.R_used * a.Fh;
     const int tiles = ceil_div(M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
     const int grid = 2 * (tiles < pairs ? tiles : pairs);
-    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, ta /*unused: direct epilogue*/, ta, M, a.N, loader, epi));
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, ta /*unused: direct epilogue*/, ta, M, a.N, loader, epi, Q8Scales{}));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;

@@ -69,14 +69,53 @@ static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t strea
     LoaderLinear loader{ceil_div(a.K, kBlockK)};
     const int tiles = ceil_div(a.M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
     const int grid = 2 * (tiles < pairs ? tiles : pairs);
-    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, tc_, tc2, a.M, a.N, loader, epi));
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, tc_, tc2, a.M, a.N, loader, epi, Q8Scales{}));
+    ++g_launch_counter;
+    Q3A_CUDA(cudaGetLastError());
+    return Q3A_OK;
+}
+
+// Q8_0 weights, dequantised inside the kernel (gemm_tc.cuh, kWq8): the W tensor map covers the int8 plane
+template <int BLOCK_N, int kFmt, class Epi>
+static int launch_linear_q8(const LinearArgs& a, const Epi& epi, cudaStream_t stream) {
+    using S = GemmSmemFor<BLOCK_N, Epi, true>;
+    CUtensorMap ta, tb, tc_;
+    Q3A_TRY(make_tmap_2d(&ta, a.a, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, kBlockM));
+    Q3A_TRY(make_tmap_u8_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldw, BLOCK_N / 2));
+    Q3A_TRY(make_tmap_tile32(&tc_, a.out, Epi::kOutBytes, (uint64_t)a.M, (uint64_t)a.N, (uint64_t)a.ldc));
+    auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderLinear, Epi, true>;
+    int pairs = 0;
+    Q3A_TRY(gemm_prepare_impl(reinterpret_cast<const void*>(kern), S::kTotal, kGemmThreads + 32 * kDequantWarps, &pairs));
+    LoaderLinear loader{ceil_div(a.K, kBlockK)};
+    const int tiles = ceil_div(a.M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
+    const int grid = 2 * (tiles < pairs ? tiles : pairs);
+    Q8Scales q8{static_cast<const __half*>(a.w_d), a.K / 32};
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads + 32 * kDequantWarps), S::kTotal, stream, ta, tb, tc_, tc_, a.M, a.N,
+                        loader, epi, q8));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;
 }
 
 template <int BLOCK_N, int kFmt>
+static int dispatch_epi_q8(EpiKind kind, const LinearArgs& a, cudaStream_t stream) {
+    using OpT = typename std::conditional<kFmt == 1, __nv_bfloat16, __half>::type;
+    switch (kind) {
+        case EPI_BIAS_OP: return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, false>{a.bias}, stream);
+        case EPI_BIAS_GELU_OP: return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasActOp<OpT, true>{a.bias}, stream);
+        case EPI_BIAS_F32: return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasF32<false>{a.bias}, stream);
+        case EPI_BIAS_RES_F32:
+            if (a.res != a.out) { set_error("gemm_linear: the residual must be the output matrix (updated in place)"); return Q3A_ERR_ARG; }
+            return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias}, stream);
+        default: break;
+    }
+    set_error("gemm_linear: this epilogue has no fused-Q8_0 instantiation");
+    return Q3A_ERR_ARG;
+}
+
+template <int BLOCK_N, int kFmt>
 static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) {
+    if (a.w_d) return dispatch_epi_q8<BLOCK_N, kFmt>(kind, a, stream);
     using OpT = typename std::conditional<kFmt == 1, __nv_bfloat16, __half>::type;
     switch (kind) {
         case EPI_BIAS_OP:
@@ -127,6 +166,7 @@ int gemm_linear(EpiKind kind, int fmt, const LinearArgs& a, cudaStream_t stream)
         set_error("gemm_linear: K, N and leading dimensions must be positive multiples of 8");
         return Q3A_ERR_ARG;
     }
+    if (a.w_d && (a.K % 64 || a.ldw != a.K)) { set_error("gemm_linear: fused Q8_0 weights need K % 64 == 0 and a dense int8 plane"); return Q3A_ERR_ARG; }
     int bn = a.block_n ? a.block_n : pick_block_n(a.N);
     if (bn == 240) bn = 128;
     return fmt == OP_F16 ? dispatch_bn<0>(kind, a, bn, stream) : dispatch_bn<1>(kind, a, bn, stream);

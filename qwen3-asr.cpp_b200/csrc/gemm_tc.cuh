@@ -18,6 +18,10 @@
 //                the residual stream is brought in by TMA loads one chunk ahead.  The convolution
 //                epilogues scatter rows and store straight from registers instead.
 //
+//   warps 12..15 (kWq8 only) fused Q8_0 dequantisation: the W tile arrives as int8 (TMA, raw ring), these warps expand
+//                it -- value = d * q per 32-element block, ggml's Q8_0 definition -- into the swizzled 16-bit
+//                operand stage the MMA reads, and signal the "full" barrier next to the A tile's TMA bytes
+//
 // Both operands are K-major 16-bit (bf16 or f16) staged with 128-byte swizzle, K blocks of 64.  The A-side
 // coordinates come from a "loader" policy so the same kernel runs the Linear layers (2-D tensor map) and
 // the stride-2 3x3 convolutions of the stem as implicit GEMM (4-D tensor map over parity-split
@@ -34,16 +38,18 @@ constexpr int kBlockM = 128;                // rows per CTA; a pair covers 256
 constexpr int kBlockK = 64;                 // 64 x 16-bit = 128 B = one swizzle span
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 384;           // 4 control warps + 8 epilogue warps
+constexpr int kDequantWarps = 4;            // Q8_0 weight path: + 4 warps that expand int8 blocks into the operand stage
 constexpr int kEpiWarps = 8;
 constexpr int kTmemCols = 512;              // two accumulator buffers of up to 256 columns
 constexpr int kSmemLimit = 232448;          // 227 KB opt-in maximum per CTA
 
 // kEpiBufBytes: bytes of one epilogue staging buffer set (32 rows; a dual-output epilogue stages the f32 chunk and its
 // 16-bit copy), kEpiBufs: buffer sets per epilogue warp
-template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs> struct GemmSmem {
+template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs, bool kWq8 = false> struct GemmSmem {
     static constexpr int kABytes = kBlockM * kBlockK * 2;              // 16 KB
     static constexpr int kBBytes = (BLOCK_N / 2) * kBlockK * 2;        // this CTA's half of the W tile
-    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kRawBytes = kWq8 ? (BLOCK_N / 2) * kBlockK : 0;   // the same half as int8 (Q8_0 weights)
+    static constexpr int kStageBytes = kABytes + kBBytes + kRawBytes;
     static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;
     static constexpr int kBarrierBytes = 512;
     static constexpr int kAvail = kSmemLimit - 1024 - kBarrierBytes - kEpiBytes;
@@ -54,9 +60,9 @@ template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs> struct GemmSmem {
 };
 // the shared-memory plan of a (BLOCK_N, epilogue) instantiation, for kernel and host alike
 template <class Epi> struct EpiDual { static constexpr bool value = false; };     // specialised by dual-output epilogues
-template <int BLOCK_N, class Epi>
+template <int BLOCK_N, class Epi, bool kWq8 = false>
 using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes + (EpiDual<Epi>::value ? 32 * 32 * 2 : 0) : 0,
-                             Epi::kStaged ? (Epi::kResidual && !EpiDual<Epi>::value ? 3 : 2) : 0>;
+                             Epi::kStaged ? (Epi::kResidual && !EpiDual<Epi>::value ? 3 : 2) : 0, kWq8>;
 // per-row state an epilogue may carry across the column chunks of a tile (LayerNorm-folded epilogues keep mean / rstd)
 struct NoRowState {};
 template <class Epi, class = void> struct EpiRowState { using type = NoRowState; };
@@ -112,6 +118,13 @@ __device__ __forceinline__ uint32_t stage_off(int r, int j) {
     return (uint32_t)(r * 64 + ((j ^ ((r >> 1) & 3)) << 4));
 }
 
+// Q8_0 weights as they sit in device memory (de-interleaved ggml blocks: the int8 plane is read through tmap_b, the
+// scales straight from global memory): scale of element (n, k) = d[n * ld_d + k / 32]
+struct Q8Scales {
+    const __half* d = nullptr;
+    int ld_d = 0;               // K / 32
+};
+
 // ---- the kernel ------------------------------------------------------------------------------
 // Epilogue contracts (epilogues.cuh):
 //   staged   struct E { static constexpr bool kStaged = true; using OutT = float | bf16 | f16;
@@ -127,11 +140,11 @@ __device__ __forceinline__ uint32_t stage_off(int r, int j) {
 //   direct   struct E { static constexpr bool kStaged = false;
 //                       __device__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const; }
 //            called for rows m < M; only the first nvalid (multiple of 8) columns belong to the output.
-template <int BLOCK_N, int kFmt, class Loader, class Epilogue>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+template <int BLOCK_N, int kFmt, class Loader, class Epilogue, bool kWq8 = false>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads + (kWq8 ? 32 * kDequantWarps : 0), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c2, int M, int N,
-               Loader loader, Epilogue epi) {
+               Loader loader, Epilogue epi, Q8Scales q8 = Q8Scales{}) {
     constexpr bool kStaged = Epilogue::kStaged;
     constexpr bool kResidual = Epilogue::kResidual;
     constexpr bool kDual = EpiDual<Epilogue>::value;
@@ -145,7 +158,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     // waits for the store of chunk i-1 to have READ its buffer (lane 0 only, ~100 clk, under the other lanes' tcgen05.ld) --
     // so that the stage ring keeps its depth.
     constexpr int kEpiBufs = kStaged ? (kResidual && !kDual ? 3 : 2) : 0;
-    using S = GemmSmemFor<BLOCK_N, Epilogue>;
+    using S = GemmSmemFor<BLOCK_N, Epilogue, kWq8>;
     constexpr int kStages = S::kStages;
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "BLOCK_N must be a multiple of 16, at most 256");
     static_assert(!kStaged || BLOCK_N % 32 == 0, "staged epilogues store whole 32-column chunks");
@@ -162,7 +175,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
     auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * kStages + 5 + w * 3 + b); };   // 24 barriers
-    static_assert(8 * (2 * 6 + 5 + 24) <= S::kBarrierBytes, "barrier block too small");
+    auto raw_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 5 + 24 + s); };             // Q8 raw ring
+    static_assert(8 * (2 * 6 + 5 + 24 + 6) <= S::kBarrierBytes, "barrier block too small");
     volatile uint32_t* tmem_slot_ptr =
         reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + S::kEpiBytes + 8 * (2 * kStages + 4));
 
@@ -181,7 +195,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         if (kDual) tc::prefetch_tmap(&tmap_c2);
     }
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < kStages; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), 1); }
+        // Q8 path: the dequant warps of both CTAs arrive on the leader's "full" barrier next to the producer's expect_tx
+        for (int s = 0; s < kStages; ++s) {
+            tc::mbar_init(full_bar(s), kWq8 ? 1 + 2 * kDequantWarps : 1); tc::mbar_init(empty_bar(s), 1);
+            if (kWq8) tc::mbar_init(raw_bar(s), 1);
+        }
         for (int s = 0; s < 2; ++s) { tc::mbar_init(tfull_bar(s), 1); tc::mbar_init(tempty_bar(s), 2 * kEpiWarps); }
         for (int w = 0; w < kEpiWarps; ++w)
             for (int b = 0; b < 3; ++b) tc::mbar_init(res_bar(w, b), 1);
@@ -209,10 +227,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 tc::mbar_wait(empty_bar(s), ph ^ 1);
                 if (tc::elect_one()) {
                     const uint32_t a_dst = smem_base + s * S::kStageBytes;
-                    if (rank == 0) tc::mbar_arrive_expect_tx(full_bar(s), 2 * S::kStageBytes);
                     const uint32_t bar = tc::mapa(full_bar(s), 0);
-                    loader.load_a(a_dst, &tmap_a, bar, m128, li);
-                    tc::tma_load_2d_pair(a_dst + S::kABytes, &tmap_b, bar, kb * kBlockK, b_row);
+                    if constexpr (!kWq8) {
+                        if (rank == 0) tc::mbar_arrive_expect_tx(full_bar(s), 2 * S::kStageBytes);
+                        loader.load_a(a_dst, &tmap_a, bar, m128, li);
+                        tc::tma_load_2d_pair(a_dst + S::kABytes, &tmap_b, bar, kb * kBlockK, b_row);
+                    } else {
+                        // A goes to the operand stage as usual; W arrives as int8 in this CTA's raw buffer (own barrier)
+                        if (rank == 0) tc::mbar_arrive_expect_tx(full_bar(s), 2 * S::kABytes);
+                        loader.load_a(a_dst, &tmap_a, bar, m128, li);
+                        tc::mbar_arrive_expect_tx(raw_bar(s), S::kRawBytes);
+                        tc::tma_load_2d(a_dst + S::kABytes + S::kBBytes, &tmap_b, raw_bar(s), kb * kBlockK, b_row);
+                    }
                 }
                 __syncwarp();
                 loader.next(li);
@@ -258,7 +284,66 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 __syncwarp();
             }
         }
-    } else if (warp >= 4) {
+    } else if (kWq8 && warp >= 4 + kEpiWarps) {
+        // ===================== Q8_0 dequantisation (both CTAs): raw int8 tile -> swizzled 16-bit operand tile =========
+        // One W row per thread: 64 int8 (4 x LDS.128, chunk order rotated by row so that a quarter-warp hits eight
+        // different 16-byte bank groups) -> value = d * q exactly as ggml defines Q8_0 (one f32 rounding-free product:
+        // with x = 1 + (q+128) * 2^-15 built by a byte permute, fma(x, 2^15 d, -(2^15 + 128) d) = q * d exactly) ->
+        // rounded once to the operand type, the same value the dequantise-at-load path stores -> 8 x STS.128 into the
+        // 128-byte-swizzled K-major layout (conflict-free by construction).
+        using OpT = typename std::conditional<kFmt == 1, __nv_bfloat16, __half>::type;
+        const int r = (warp - 4 - kEpiWarps) * 32 + lane;                  // row of this CTA's half tile
+        const bool has_row = r < BLOCK_N / 2;
+        const uint32_t full_leader0 = tc::mapa(full_bar(0), 0);
+        int s = 0;
+        uint32_t ph = 0;
+        for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+            const int m_blk = tile / n_blocks, n_blk = tile - m_blk * n_blocks;
+            const int n = n_blk * BLOCK_N + (int)rank * (BLOCK_N / 2) + r;
+            const bool live = has_row && n < N;
+            const uint32_t* drow = reinterpret_cast<const uint32_t*>(q8.d + (size_t)(live ? n : 0) * q8.ld_d);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                const uint32_t dd = live ? __ldg(drow + kb) : 0u;          // the two block scales of this K block (f16 pair)
+                tc::mbar_wait(raw_bar(s), ph);
+                if (has_row) {
+                    const uint8_t* stage = smem_gen + s * S::kStageBytes;
+                    const uint8_t* raw = stage + S::kABytes + S::kBBytes + r * 64;
+                    uint8_t* dst = const_cast<uint8_t*>(stage) + S::kABytes + r * 128;
+                    const __half2 dh = *reinterpret_cast<const __half2*>(&dd);
+                    const float d0 = __low2float(dh), d1 = __high2float(dh);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int c = (i + (r >> 1)) & 3;                   // 16 int8 = elements 16c .. 16c+15 of the K block
+                        const uint4 qv = *reinterpret_cast<const uint4*>(raw + c * 16);
+                        const float dsc = c < 2 ? d0 : d1;
+                        const float mul = dsc * 32768.0f, add = -(32768.0f + 128.0f) * dsc;
+                        const uint32_t w4[4] = {qv.x ^ 0x80808080u, qv.y ^ 0x80808080u, qv.z ^ 0x80808080u, qv.w ^ 0x80808080u};
+                        float f[16];
+#pragma unroll
+                        for (int e = 0; e < 16; ++e) {
+                            // byte e of the chunk into bits [8,16) of 0x3F800000: 1 + u8 * 2^-15
+                            const uint32_t bits = __byte_perm(w4[e >> 2], 0x3F800000u, 0x7604 | ((e & 3) << 4));
+                            f[e] = fmaf(__uint_as_float(bits), mul, add);
+                        }
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            uint4 u;
+                            u.x = OpTraits<OpT>::pack2(f[8 * h + 0], f[8 * h + 1]);
+                            u.y = OpTraits<OpT>::pack2(f[8 * h + 2], f[8 * h + 3]);
+                            u.z = OpTraits<OpT>::pack2(f[8 * h + 4], f[8 * h + 5]);
+                            u.w = OpTraits<OpT>::pack2(f[8 * h + 6], f[8 * h + 7]);
+                            const int j = 2 * c + h;                        // 16-byte chunk of the 128-byte operand row
+                            *reinterpret_cast<uint4*>(dst + ((j ^ (r & 7)) << 4)) = u;
+                        }
+                    }
+                }
+                tc::fence_proxy_async();                                    // generic-proxy writes -> visible to the tensor cores
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive_cluster(full_leader0 + 8u * s);
+                if (++s == kStages) { s = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp >= 4 && warp < 4 + kEpiWarps) {
         // ===================== epilogue (both CTAs) =====================
         const int ew = warp - 4;
         const int q = warp & 3;                       // TMEM lane quadrant this warp may read

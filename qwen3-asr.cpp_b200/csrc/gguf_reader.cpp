@@ -177,4 +177,19 @@ bool GgufFile::read_f32(const GgufTensor& t, std::vector<float>& out, std::strin
     return true;
 }
 
+bool GgufFile::read_q8_planes(const GgufTensor& t, std::vector<int8_t>& q, std::vector<uint16_t>& d, std::string& err) const {
+    if (t.type != GGML_Q8_0) { err = "tensor " + t.name + " is not Q8_0"; return false; }
+    const int64_t n = t.n_elements();
+    if (t.ne.empty() || t.ne[0] % 32) { err = "Q8_0 tensor with a row length not a multiple of 32: " + t.name; return false; }
+    const size_t bytes = (size_t)(n / 32) * 34;
+    if (data_start_ + t.offset + bytes > map_size_) { err = "tensor data out of file bounds: " + t.name; return false; }
+    const uint8_t* src = static_cast<const uint8_t*>(map_) + data_start_ + t.offset;
+    q.resize((size_t)n); d.resize((size_t)(n / 32));
+    for (int64_t b = 0; b < n / 32; ++b) {                 // { f16 d; int8 q[32]; }
+        std::memcpy(&d[b], src + b * 34, 2);
+        std::memcpy(&q[b * 32], src + b * 34 + 2, 32);
+    }
+    return true;
+}
+
 }  // namespace q3a

@@ -31,6 +31,8 @@ public:
     float get_f32(const std::string& key, float dflt) const;
     // dequantise a tensor to f32 (F32 / F16 / BF16 / Q8_0); false if the type is unsupported or the data is truncated
     bool read_f32(const GgufTensor& t, std::vector<float>& out, std::string& err) const;
+    // Q8_0 tensor as two planes: q[n_elements] int8 and d[n_elements / 32] f16 bit patterns (ggml block order kept)
+    bool read_q8_planes(const GgufTensor& t, std::vector<int8_t>& q, std::vector<uint16_t>& d, std::string& err) const;
     const std::vector<GgufTensor>& tensors() const { return tensors_; }
 
 private:

@@ -64,6 +64,23 @@ int make_tmap_tile32(CUtensorMap* out, const void* base, int elem_bytes, uint64_
     return Q3A_OK;
 }
 
+int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+    std::call_once(g_once, resolve);
+    if (!g_encode) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return Q3A_ERR_CUDA; }
+    cuuint64_t d[2] = {cols, rows};
+    cuuint64_t s[1] = {ld};
+    cuuint32_t b[2] = {64, box_rows};
+    cuuint32_t es[2] = {1, 1};
+    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), d, s, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled (int8 plane) failed with code " + std::to_string((int)r) + " rows " + std::to_string(rows) +
+                  " cols " + std::to_string(cols));
+        return Q3A_ERR_CUDA;
+    }
+    return Q3A_OK;
+}
+
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
     uint64_t dims[2] = {cols, rows};
     uint64_t strides[1] = {ld * 2};

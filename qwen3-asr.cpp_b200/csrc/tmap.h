@@ -19,4 +19,7 @@ int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t col
 // bytes (64 B for 16-bit, 128 B for f32): the GEMM epilogue's staged stores and residual loads
 int make_tmap_tile32(CUtensorMap* out, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld);
 
+// row-major [rows][cols] int8 matrix (Q8_0 weight plane), box = {64 bytes, box_rows}, no swizzle: the dequant warps read it
+int make_tmap_u8_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows);
+
 }  // namespace q3a

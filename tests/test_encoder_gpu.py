@@ -467,3 +467,32 @@ def test_q8_file_three_way_at_real_width(lib, asr_model, filters):
         assert cos_ab >= COS and rel_ab <= REL, (cos_ab, rel_ab)
         assert cos_cb >= COS and rel_cb <= 3e-2, (cos_cb, rel_cb)
         assert cos_ac >= COS and rel_ac <= rel_ab + rel_cb + 1e-3, (cos_ac, rel_ac)
+
+
+def test_q8_fused_dequant_is_bit_identical_to_dequant_at_load(lib, tiny_models, asr_model, filters, monkeypatch):
+    """Row a12: with a Q8_0 file the Linear weights stay quantised in device memory (int8 plane + f16 block scales, 34 bytes
+    per 32 weights as in the GGUF) and the GEMM's dequant warps expand them into the operand stage.  The value they
+    produce is d * q rounded once to the operand type -- exactly what expanding at load time stores -- so the two paths
+    must agree bit for bit (same LayerNorm kernel path on both sides); and the resident weights must be about half."""
+    _, models = tiny_models
+    shape, paths, _ = asr_model
+    mels_tiny = _mels(filters)[:4]
+    mel_big = MO.log_mel_numpy(synth.synth_audio(303, 16000 * 7 + 123), filters)
+    for path, mels, opd in ((models["q8_0"][0], mels_tiny, B.OP_F16), (models["q8_0"][0], mels_tiny, B.OP_BF16),
+                            (paths["q8_0"], [mel_big], B.OP_BF16)):
+        fused = B.Encoder(path, 0, opd)
+        bytes_fused = fused.device_bytes()
+        got = fused.encode_batch(mels, B.MODE_ASR)
+        fused.close()
+        monkeypatch.setenv("Q3A_Q8_DEQUANT_AT_LOAD", "1")
+        monkeypatch.setenv("Q3A_NO_LN_FOLD", "1")
+        plain = B.Encoder(path, 0, opd)
+        monkeypatch.delenv("Q3A_Q8_DEQUANT_AT_LOAD"); monkeypatch.delenv("Q3A_NO_LN_FOLD")
+        bytes_plain = plain.device_bytes()
+        want = plain.encode_batch(mels, B.MODE_ASR)
+        plain.close()
+        for a, b in zip(got, want):
+            assert a.shape == b.shape and np.array_equal(a, b)
+        if path == paths["q8_0"]:
+            print(f"ASR-0.6B weight arena: Q8_0 resident {bytes_fused / 1e6:.1f} MB vs expanded to 16 bit {bytes_plain / 1e6:.1f} MB")
+            assert bytes_fused < 0.62 * bytes_plain
