@@ -190,6 +190,121 @@ def run_reference(args):
     print(json.dumps(line), file=_OUT, flush=True)
 
 
+# ------------------------------------------------------------------------------------------------ sharded corpus
+CORPUS_SECONDS = 36000.0          # BASELINE.json configs[4]: 10 h, utterances log-uniform 2-60 s, seed 500
+CORPUS_SEED = 500
+
+
+def corpus_lengths(total_s: float = CORPUS_SECONDS, seed: int = CORPUS_SEED):
+    """Sample counts of the synthetic long-form corpus: log-uniform 2-60 s until `total_s` is reached; not multiples of 160."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    out, tot = [], 0.0
+    while tot < total_s:
+        sec = float(np.exp(rng.uniform(np.log(2.0), np.log(60.0))))
+        out.append(int(sec * SR) + int(rng.integers(0, 160)))
+        tot += sec
+    return out
+
+
+def corpus_utterance(base, i: int, n: int):
+    """Utterance i of the corpus, identical on whichever rank builds it: a shifted, scaled cut of a 60-s synthetic signal."""
+    import numpy as np
+    rng = np.random.default_rng([CORPUS_SEED, i])
+    return (np.roll(base, int(rng.integers(0, len(base))))[:n] * np.float32(rng.uniform(0.5, 1.0))).astype(np.float32)
+
+
+def corpus_plan(B, rank: int, world: int):
+    """(sample counts, utterances this rank owns, utterances of the next rank it re-encodes as a cross-check)"""
+    lens = corpus_lengths()
+    plan = B.plan_shards([n // 160 for n in lens], B.MODE_ASR, world)
+    mine = [i for i, s in enumerate(plan) if s == rank]
+    theirs = [i for i, s in enumerate(plan) if s == (rank + 1) % world][:8] if world > 1 else mine[:8]
+    return lens, mine, theirs
+
+
+def corpus_verdict(gathered):
+    """gathered: per rank ({utterance: digest} of its own shard, {utterance: digest} of its cross-checks) ->
+    (every cross-check equals the owner's digest, number of cross-checks, utterances owned exactly once)"""
+    owner, owned = {}, 0
+    for o, _ in gathered:
+        owned += len(o)
+        owner.update(o)
+    checked = sum(len(c) for _, c in gathered)
+    identical = all(owner.get(i) == h for _, c in gathered for i, h in c.items())
+    return identical, checked, owned == len(owner)
+
+
+def run_corpus(enc, fe, B, synth, rank: int, world: int, dist, torch):
+    """configs[4] on hardware: every rank derives the same LPT plan (q3a_plan_shards), encodes only its own shard through
+    the host-pointer call, and the job's time is the slowest rank's.  Determinism: every rank also encodes 8 utterances
+    owned by the next rank, in a different batch; their SHA-256 must equal the owner's."""
+    import ctypes as C
+    import hashlib
+    import numpy as np
+    lens, mine, theirs = corpus_plan(B, rank, world)
+    base = synth.synth_audio(CORPUS_SEED, 60 * SR + 159)
+    width = enc.hp.out_dim
+
+    def stage(ids):
+        ns = [lens[i] for i in ids]
+        toks = [enc.n_tokens(n // 160) for n in ns]
+        pcm = torch.empty(sum(ns), dtype=torch.float32).pin_memory()
+        out = torch.empty((sum(toks), width), dtype=torch.float32).pin_memory()
+        pv, po, pp, op = pcm.numpy(), 0, [], []
+        ro = 0
+        for i, n, t in zip(ids, ns, toks):
+            pv[po:po + n] = corpus_utterance(base, i, n)
+            pp.append(pcm.data_ptr() + 4 * po); op.append(out.data_ptr() + 4 * width * ro)
+            po += n; ro += t
+        return pcm, out, ns, toks, (C.c_void_p * len(ids))(*pp), (C.c_void_p * len(ids))(*op), (C.c_int * len(ids))(*ns)
+
+    def encode(st):
+        pcm, out, ns, toks, pp, op, na = st
+        ntok = (C.c_int * len(ns))()
+        B.check(enc.lib.q3a_encode_pcm_batch(fe.h, enc.h, pp, na, len(ns), B.MODE_ASR, op, ntok))
+        assert list(ntok) == toks
+
+    def digests(st, ids):
+        out, toks = st[1].numpy(), st[3]
+        d, r = {}, 0
+        for i, t in zip(ids, toks):
+            d[i] = hashlib.sha256(out[r:r + t].tobytes()).hexdigest()
+            r += t
+        return d
+
+    st_mine, st_theirs = stage(mine), stage(theirs)
+    encode(st_mine)                                   # warm-up: workspace growth, first-touch of the pinned pages
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    encode(st_mine)
+    dt = time.perf_counter() - t0
+    encode(st_theirs)
+    own, chk = digests(st_mine, mine), digests(st_theirs, theirs)
+    t = torch.tensor([dt], device="cuda")
+    tmax, tsum = t.clone(), t.clone()
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (own, chk))
+    else:
+        gathered = [(own, chk)]
+    identical, checked, partition_ok = corpus_verdict(gathered)
+    identical = identical and partition_ok and sum(len(o) for o, _ in gathered) == len(lens)
+    makespan = float(tmax.item())
+    audio_s = sum(lens) / SR
+    return {"workload": "BASELINE.json configs[4]: 10-h synthetic corpus, utterances log-uniform 2-60 s (seed 500), ASR-0.6B bf16, "
+                        "sharded by utterance with q3a_plan_shards (LPT), one q3a_encode_pcm_batch call per rank, pinned host "
+                        "PCM in / pinned host features out",
+            "utterances": len(lens), "audio_seconds": audio_s, "n_gpus": world, "makespan_s": makespan,
+            "audio_s_per_s": audio_s / makespan, "rank_time_max_over_mean": makespan / (float(tsum.item()) / world),
+            "utterances_this_rank": len(mine), "bit_identical": bool(identical), "cross_checked_utterances": checked,
+            "check": "SHA-256 of 8 utterances per rank re-encoded by the next rank in a different batch vs the owner's"}
+
+
 # ------------------------------------------------------------------------------------------------ GPU arm
 def run_ours(args):
     import numpy as np
@@ -312,6 +427,12 @@ def run_ours(args):
         raise SystemExit(f"bench.py: q3a_encode_pcm_device output differs from q3a_encode_pcm_batch on rank {rank} "
                          f"(finite={finite}, max |diff| = {max_diff}) -- the timed value is void")
 
+    corpus = None
+    if not args.no_corpus:
+        corpus = run_corpus(enc, fe, B, synth, rank, world, dist, torch)
+        if not corpus["bit_identical"]:
+            raise SystemExit("bench.py: sharded-corpus determinism check failed: an utterance's features depend on the rank / batch")
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -389,6 +510,8 @@ def run_ours(args):
         "whole_step_tflops": ASR_GFLOP_PER_30S * BATCH * args.steps * world / (ms_total / 1e3) / 1e3,
         "device_bytes": enc.device_bytes(),
     }
+    if corpus is not None:
+        line["corpus"] = corpus
     if cpu is not None:
         line["cpu_baseline"] = cpu
     print(json.dumps(line), file=_OUT, flush=True)
@@ -407,6 +530,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~20 s CPU baseline leg (profiling runs)")
+    ap.add_argument("--no-corpus", action="store_true", help="skip the sharded 10-h corpus leg (profiling runs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) go to stderr

@@ -20,6 +20,7 @@
 #ifndef Q3A_H
 #define Q3A_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -180,6 +181,26 @@ int64_t q3a_encoder_device_bytes(const q3a_encoder* enc);
 /* Longest-processing-time assignment of utterances to n_shards replicas by predicted cost
  * a*T + b*sum(seg^2); shard_of[i] receives the shard of utterance i.  Deterministic. Host only. */
 int q3a_plan_shards(const int* n_frames, int n_utts, int mode, int n_shards, int* shard_of);
+
+/* ---- in-process multi-GPU executor (csrc/pool.cu) ------------------------------------------------------------
+ * The reference is a single process that encodes one utterance at a time (qwen3_asr.cpp:81-149, main.cpp:294-504).  A
+ * pool holds one replica (frontend + encoder) and one host worker thread per listed device; q3a_pool_encode_pcm is
+ * q3a_encode_pcm_batch for a whole corpus: utterances are assigned to the replicas by q3a_plan_shards, every replica
+ * encodes its shard with its own streams, features land in out[i] -- utterance order -- and are bit-identical to what
+ * any single replica computes for that utterance.  No collective, no device-to-device traffic.  shard_of (n_clips)
+ * and shard_ms (n_devices: wall time of every replica's call) may be NULL.  A device may be listed more than once. */
+typedef struct q3a_pool q3a_pool;
+int q3a_pool_create(const char* gguf_path, const int* devices, int n_devices, int operand_dtype, q3a_pool** out);
+void q3a_pool_free(q3a_pool* pool);
+int q3a_pool_n_devices(const q3a_pool* pool);
+int q3a_pool_encode_pcm(q3a_pool* pool, const float* const* pcm, const int* n_samples, int n_clips, int mode,
+                        float* const* out, int* n_tokens, int* shard_of, float* shard_ms);
+/* Host placement helpers for callers of the host-pointer entry points: pinned (portable) staging memory, and binding
+ * the calling thread to the CPUs local to a GPU (from /sys/bus/pci/devices/<bus id>/local_cpulist; returns the number
+ * of CPUs bound, 0 if nothing was changed).  The pool's workers bind themselves. */
+int q3a_host_alloc(size_t bytes, void** out);
+void q3a_host_free(void* p);
+int q3a_bind_thread_to_device(int device);
 
 /* How a q3a_encode_pcm_batch call over these clips is scheduled: pass_of[i] (a pass bounds the stem workspace;
  * consecutive passes overlap as upload | compute | download), in_part_of[i] (upload part inside the pass: the stem of a

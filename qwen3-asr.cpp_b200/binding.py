@@ -64,6 +64,13 @@ SYMBOLS = {
     "q3a_encoder_get_timings": (_I, [_P, C.POINTER(Timings)]),
     "q3a_encoder_device_bytes": (_I64, [_P]),
     "q3a_plan_shards": (_I, [_P, _I, _I, _I, _P]),
+    "q3a_pool_create": (_I, [C.c_char_p, _P, _I, _I, C.POINTER(_P)]),
+    "q3a_pool_free": (None, [_P]),
+    "q3a_pool_n_devices": (_I, [_P]),
+    "q3a_pool_encode_pcm": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _P]),
+    "q3a_host_alloc": (_I, [C.c_size_t, C.POINTER(_P)]),
+    "q3a_host_free": (None, [_P]),
+    "q3a_bind_thread_to_device": (_I, [_I]),
     "q3a_plan_host_call": (_I, [_P, _I, _I, _I, _P, _P, _P]),
     "q3a_test_gemm": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "q3a_test_attention": (_I, [_P, _P, _I, _I, _P, _I, _I, _P]),
@@ -246,6 +253,43 @@ class Encoder:
 
     def device_bytes(self) -> int:
         return int(self.lib.q3a_encoder_device_bytes(self.h))
+
+
+class Pool:
+    """q3a_pool: one replica + one worker thread per listed device (a device may repeat); corpus in, features out in
+    utterance order."""
+
+    def __init__(self, gguf_path: str, devices, operand: int = OP_BF16):
+        self.lib = load()
+        self.h = C.c_void_p()
+        self.devices = list(devices)
+        check(self.lib.q3a_pool_create(gguf_path.encode(), _int_array(self.devices), len(self.devices), operand, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            self.lib.q3a_pool_free(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def encode_pcm(self, clips, mode: int = MODE_ASR, out_dim: int = 1024, outs=None):
+        """-> (features per clip, shard of every clip, wall ms of every replica).  `outs`: preallocated arrays to fill."""
+        clips = [np.ascontiguousarray(c, dtype=np.float32) for c in clips]
+        n = [len(c) for c in clips]
+        lib = self.lib
+        if outs is None:
+            outs = [np.zeros((max(lib.q3a_encoder_n_tokens(k // 160, mode), 0), out_dim), dtype=np.float32) for k in n]
+        n_tok = (C.c_int * max(len(clips), 1))()
+        shard = (C.c_int * max(len(clips), 1))()
+        ms = (C.c_float * len(self.devices))()
+        check(lib.q3a_pool_encode_pcm(self.h, _ptr_array(clips), _int_array(n), len(clips), mode, _ptr_array(outs), n_tok, shard, ms))
+        for o, k in zip(outs, n_tok):
+            assert o.shape[0] == k, (o.shape, k)
+        return outs, list(shard)[:len(clips)], list(ms)
 
 
 def plan_host_call(n_samples, mode: int, out_width: int = 1024) -> tuple[list[int], list[int], list[int]]:

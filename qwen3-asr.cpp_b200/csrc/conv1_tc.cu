@@ -273,18 +273,10 @@ int conv1_tc_launch(const float* mel, const StemChunk* chunks_dev, int n_chunks,
                              (uint64_t)C, (uint64_t)C));
     auto kern = conv1_tc_kernel<OpT>;
     const int smem = c1_smem_bytes(C);
-    static bool attr_done[64] = {false};
-    int dev = 0;
-    Q3A_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        Q3A_CUDA(cudaFuncSetAttribute(conv1_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, c1_smem_bytes(512)));
-        Q3A_CUDA(cudaFuncSetAttribute(conv1_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, c1_smem_bytes(512)));
-        attr_done[dev] = true;
-    }
+    Q3A_TRY(kernel_smem_optin(reinterpret_cast<const void*>(kern), c1_smem_bytes(512)));   // per (kernel, device), thread-safe
     const int tpc = P2 - 1;
     const int n_tiles = n_chunks * tpc;
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int sms = sm_count_cached();
     const int grid = n_tiles < sms ? n_tiles : sms;
     Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kC1Threads), smem, stream, mel, chunks_dev, n_tiles, tpc, P2, clip_max,
                         reinterpret_cast<const uint4*>(w_image), bias, C, tm, rows_per_plane));
