@@ -158,6 +158,12 @@ int q3a_encoder_encode_device(q3a_encoder* enc, const float* mel_dev, const int6
  * (qwen3_asr.cpp:90,105) / ForcedAligner::align's (forced_aligner.cpp:1653,1661) for a batch. */
 int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* enc, const float* const* pcm, const int* n_samples,
                          int n_clips, int mode, float* const* out, int* n_tokens);
+/* asynchronous twin: submit enqueues the call and returns a ticket, q3a_encode_wait blocks until that call (and every
+ * earlier one) has delivered its features.  Up to two calls overlap: call k+1 uploads and runs its stem under call k's last
+ * layers and download.  pcm[i] / out[i] must stay valid until the wait returns; n_tokens is final when submit returns. */
+int q3a_encode_pcm_submit(q3a_frontend* fe, q3a_encoder* enc, const float* const* pcm, const int* n_samples,
+                          int n_clips, int mode, float* const* out, int* n_tokens, int64_t* ticket);
+int q3a_encode_wait(q3a_encoder* enc, int64_t ticket);
 /* same from 16-bit PCM as it sits in a WAV file: load_wav's conversion (mel_spectrogram.cpp:195-210: interleaved
  * channels averaged in float, then / 32768) runs on the device, so the upload is 2 bytes per sample.  n_samples[i]
  * counts frames (samples per channel); pcm[i] holds n_samples[i] * n_channels values; n_channels in 1..8.

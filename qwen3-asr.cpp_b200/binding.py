@@ -58,6 +58,8 @@ SYMBOLS = {
     "q3a_encoder_encode_batch": (_I, [_P, _P, _I, _P, _I, _I, _P, _P]),
     "q3a_encoder_encode_device": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
     "q3a_encode_pcm_batch": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
+    "q3a_encode_pcm_submit": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, C.POINTER(C.c_int64)]),
+    "q3a_encode_wait": (_I, [_P, C.c_int64]),
     "q3a_encode_pcm16_batch": (_I, [_P, _P, _P, _P, _I, _I, _I, _P, _P]),
     "q3a_encode_pcm_device": (_I, [_P, _P, _P, _P, _P, _I, _I, _P, _P, _P]),
     "q3a_encoder_set_profiling": (_I, [_P, _I]),

@@ -694,6 +694,7 @@ extern "C" void q3a_encoder_free(q3a_encoder* e) {
         for (auto ev : e->ev_part_in[i]) if (ev) cudaEventDestroy(ev);
         for (auto ev : e->ev_part_out[i]) if (ev) cudaEventDestroy(ev);
     }
+    for (auto ev : e->ev_done) if (ev) cudaEventDestroy(ev);
     if (e->copy_in) cudaStreamDestroy(e->copy_in);
     if (e->copy_out) cudaStreamDestroy(e->copy_out);
     if (e->stream) cudaStreamDestroy(e->stream);
@@ -728,6 +729,7 @@ extern "C" int q3a_encoder_load(const char* gguf_path, int device, int operand_d
             for (auto& ev : e->ev_part_in[i]) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
             for (auto& ev : e->ev_part_out[i]) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
         }
+        for (auto& ev : e->ev_done) ok = ok && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) == cudaSuccess;
         if (!ok) { set_error("cudaStreamCreate / cudaEventCreate failed"); rc = Q3A_ERR_CUDA; }
     }
     if (rc != Q3A_OK) { q3a_encoder_free(e); return rc; }
@@ -897,9 +899,12 @@ static void plan_host_call(const int* in_elems, int elem_bytes, int64_t align_el
     }
 }
 
+// `wait` = false: everything is enqueued and the call returns (q3a_encode_pcm_submit); the staging buffers and their events
+// are picked by a pass counter that runs across calls, so the upload of the next call overlaps the tail of this one.
 template <class Compute>
 static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_elems, int elem_bytes, int64_t align_elems,
-                           const int* n_frames, int n, int mode, int width, float* const* out, int* n_tokens, Compute compute) {
+                           const int* n_frames, int n, int mode, int width, float* const* out, int* n_tokens, Compute compute,
+                           bool wait = true) {
     static const bool trace = getenv("Q3A_TRACE") != nullptr;
     const auto t_begin = std::chrono::steady_clock::now();
     auto stamp = [&](const char* what) {
@@ -912,13 +917,14 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
     const std::vector<std::vector<int64_t>>& ioff = plan.ioff;
     const std::vector<std::vector<int>>&in_split = plan.in_split, &out_split = plan.out_split;
     const int n_pass = (int)bounds.size() - 1;
+    const long long g0 = e->pass_seq;                      // global index of this call's first pass
     DevBuf* sin[2] = {&e->stage_in, &e->stage_in2};
     DevBuf* sout[2] = {&e->stage_out, &e->stage_out2};
     size_t need_in[2] = {0, 0}, need_out[2] = {0, 0};
     for (int p = 0; p < n_pass; ++p) {
         const int nu = bounds[p + 1] - bounds[p];
-        need_in[p & 1] = std::max(need_in[p & 1], (size_t)elem_bytes * (size_t)(ioff[p][nu] + align_elems));
-        need_out[p & 1] = std::max(need_out[p & 1], sizeof(float) * ((size_t)plan.tokens[p] * width + 64));
+        need_in[(g0 + p) & 1] = std::max(need_in[(g0 + p) & 1], (size_t)elem_bytes * (size_t)(ioff[p][nu] + align_elems));
+        need_out[(g0 + p) & 1] = std::max(need_out[(g0 + p) & 1], sizeof(float) * ((size_t)plan.tokens[p] * width + 64));
     }
     for (int b = 0; b < 2; ++b) {
         if (need_in[b]) Q3A_TRY(sin[b]->reserve(need_in[b]));
@@ -931,8 +937,8 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
 #define PIPE_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error(std::string(#x) + ": " + cudaGetErrorString(e_)); return drain(Q3A_ERR_CUDA); } } while (0)
 #define HOOK_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { set_error(std::string(#x) + ": " + cudaGetErrorString(e_)); return (int)Q3A_ERR_CUDA; } } while (0)
     auto upload = [&](int p) -> int {
-        const int b = p & 1, u0 = bounds[p];
-        if (p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->copy_in, e->ev_comp[b], 0));   // pass p-2 has consumed the buffer
+        const int b = (int)((g0 + p) & 1), u0 = bounds[p];
+        if (g0 + p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->copy_in, e->ev_comp[b], 0));   // pass g-2 (maybe of an earlier call) has consumed the buffer
         const std::vector<int>& sp = in_split[p];
         for (size_t part = 0; part + 1 < sp.size(); ++part) {
             for (int i = sp[part]; i < sp[part + 1]; ++i)
@@ -947,9 +953,9 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
     if (n_pass > 0) { const int rc = upload(0); if (rc != Q3A_OK) return rc; }
     stamp("upload 0 enqueued");
     for (int p = 0; p < n_pass; ++p) {
-        const int b = p & 1, u0 = bounds[p], nu = bounds[p + 1] - u0;
+        const int b = (int)((g0 + p) & 1), u0 = bounds[p], nu = bounds[p + 1] - u0;
         if (p + 1 < n_pass) { const int rc = upload(p + 1); if (rc != Q3A_OK) return rc; }
-        if (p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->stream, e->ev_out[b], 0));       // pass p-2 has been downloaded
+        if (g0 + p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->stream, e->ev_out[b], 0));  // pass g-2 has been downloaded
         PartHooks hk;
         hk.in_split = in_split[p];
         hk.out_split = out_split[p];
@@ -977,6 +983,13 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
         PIPE_CUDA(cudaEventRecord(e->ev_comp[b], e->stream));
         PIPE_CUDA(cudaEventRecord(e->ev_out[b], e->copy_out));
     }
+    e->pass_seq += n_pass;
+    // completion of this call = its last download (the download stream waits for the compute that feeds it); an empty call
+    // completes behind whatever was submitted before it
+    PIPE_CUDA(cudaStreamWaitEvent(e->copy_out, n_pass > 0 ? e->ev_comp[(g0 + n_pass - 1) & 1] : e->ev_comp[0], 0));
+    PIPE_CUDA(cudaEventRecord(e->ev_done[e->ticket_seq % q3a_encoder::kTickets], e->copy_out));
+    ++e->ticket_seq;
+    if (!wait) { stamp("submitted"); return Q3A_OK; }
     if (trace) { cudaStreamSynchronize(e->copy_in); stamp("uploads done"); cudaStreamSynchronize(e->stream); stamp("compute done"); }
     PIPE_CUDA(cudaStreamSynchronize(e->copy_out));
     PIPE_CUDA(cudaStreamSynchronize(e->stream));
@@ -1083,6 +1096,48 @@ extern "C" int q3a_encode_pcm_batch(q3a_frontend* fe, q3a_encoder* e, const floa
                                 return pcm_core(fe, e, static_cast<const float*>(in_dev), in_off, n_samples + u0, nu, mode, out_dev, nullptr, e->stream, hk);
                             }));
     return prof_collect(e, e->stream);
+}
+
+// Asynchronous twin of q3a_encode_pcm_batch: enqueues the whole call (uploads, kernels, downloads) on the encoder's three
+// streams and returns a ticket; q3a_encode_wait blocks until that call -- and every earlier one -- has delivered its
+// features.  Two calls can be in flight (the staging buffers are double-buffered across calls): while call k runs its last
+// layers and downloads, call k+1 is already uploading and running its stem behind it on the compute stream.  pcm[i] and
+// out[i] must stay valid and untouched until the wait returns; n_tokens is filled before submit returns.
+extern "C" int q3a_encode_pcm_submit(q3a_frontend* fe, q3a_encoder* e, const float* const* pcm, const int* n_samples,
+                                     int n_clips, int mode, float* const* out, int* n_tokens, int64_t* ticket) {
+    if (!e || !fe) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (!ticket) { set_error("encode_pcm_submit: ticket is null"); return Q3A_ERR_ARG; }
+    if (mode < 0 || mode > Q3A_MODE_CONV_ONLY) { set_error("encode: unknown mode"); return Q3A_ERR_ARG; }
+    if (n_clips < 0 || (n_clips > 0 && (!pcm || !n_samples || !out))) { set_error("encode_pcm_submit: null argument"); return Q3A_ERR_ARG; }
+    for (int u = 0; u < n_clips; ++u)
+        if (n_samples[u] < 0 || (n_samples[u] > 0 && !pcm[u]) || (n_samples[u] >= 160 && !out[u])) {
+            set_error("encode_pcm_submit: bad clip " + std::to_string(u)); return Q3A_ERR_ARG;
+        }
+    Q3A_TRY(use_device(e->device));
+    if (e->profiling) { set_error("encode_pcm_submit: per-stage profiling needs the synchronous call"); return Q3A_ERR_STATE; }
+    g_launch_counter = 0;
+    prof_reset(e);
+    const int width = mode == Q3A_MODE_CONV_ONLY ? e->hp.d_model : e->hp.out_dim;
+    std::vector<int> nf(n_clips);
+    for (int i = 0; i < n_clips; ++i) nf[i] = n_samples[i] / 160;
+    // the mel staging of pcm_core is single-buffered, but it is only touched by kernels on the compute stream, which
+    // orders consecutive calls
+    Q3A_TRY(run_host_passes(e, reinterpret_cast<const void* const*>(pcm), n_samples, 4, 64, nf.data(), n_clips, mode, width, out, n_tokens,
+                            [&](int u0, int nu, const void* in_dev, const int64_t* in_off, float* out_dev, const PartHooks* hk) {
+                                return pcm_core(fe, e, static_cast<const float*>(in_dev), in_off, n_samples + u0, nu, mode, out_dev, nullptr, e->stream, hk);
+                            }, false));
+    e->tm.total_launches = g_launch_counter;
+    *ticket = e->ticket_seq - 1;
+    return Q3A_OK;
+}
+
+extern "C" int q3a_encode_wait(q3a_encoder* e, int64_t ticket) {
+    if (!e) { set_error("Model not loaded"); return Q3A_ERR_STATE; }
+    if (ticket < 0 || ticket >= e->ticket_seq) { set_error("encode_wait: unknown ticket"); return Q3A_ERR_ARG; }
+    Q3A_TRY(use_device(e->device));
+    if (e->ticket_seq - ticket > q3a_encoder::kTickets) return Q3A_OK;     // so old that its event slot was reused: long done
+    Q3A_CUDA(cudaEventSynchronize(e->ev_done[ticket % q3a_encoder::kTickets]));
+    return Q3A_OK;
 }
 
 // int16 ingest: load_wav's conversion (mel_spectrogram.cpp:195-210) on the device, so the upload carries 2 bytes per

@@ -18,6 +18,10 @@ struct q3a_encoder {
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
     static constexpr int kInParts = 4, kOutParts = 4;   // upper bounds; the split tables choose   // finer overlap inside a pass (PartHooks in encoder.cu)
     cudaEvent_t ev_part_in[2][kInParts] = {}, ev_part_out[2][kOutParts] = {};
+    long long pass_seq = 0;          // passes enqueued so far: staging buffer / event parity runs across calls
+    static constexpr int kTickets = 8;
+    cudaEvent_t ev_done[kTickets] = {};   // completion of the last kTickets host-pointer calls (q3a_encode_wait)
+    int64_t ticket_seq = 0;
 
     // ---- weights (one arena) -----------------------------------------------------------------
     q3a::DevBuf arena;

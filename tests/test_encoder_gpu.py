@@ -496,3 +496,38 @@ def test_q8_fused_dequant_is_bit_identical_to_dequant_at_load(lib, tiny_models, 
         if path == paths["q8_0"]:
             print(f"ASR-0.6B weight arena: Q8_0 resident {bytes_fused / 1e6:.1f} MB vs expanded to 16 bit {bytes_plain / 1e6:.1f} MB")
             assert bytes_fused < 0.62 * bytes_plain
+
+
+def test_async_submit_wait_matches_synchronous_call(lib, asr_model):
+    """q3a_encode_pcm_submit / q3a_encode_wait: four calls over different ragged batches with two in flight at any time
+    (call k+1 is submitted before call k is waited for, so its upload and stem overlap call k's tail); every call's
+    features equal the synchronous q3a_encode_pcm_batch result bit for bit, and an unknown ticket is refused."""
+    import ctypes as C
+    shape, paths, _ = asr_model
+    enc = B.Encoder(paths["f16"], 0, B.OP_BF16)
+    fe = B.Frontend(0)
+    rng = np.random.default_rng(21)
+    batches = [[synth.synth_audio(1200 + 10 * b + i, int(rng.integers(16000, 16000 * 25))) for i in range(5 + b)] for b in range(4)]
+    batches[2][1] = batches[2][1][:0]
+    want = [enc.encode_pcm_batch(fe, clips, B.MODE_ASR) for clips in batches]
+    keep, tickets, outs_all = [], [], []
+    for k, clips in enumerate(batches):
+        n = [len(c) for c in clips]
+        outs = [np.full((enc.n_tokens(x // 160), 1024), np.nan, np.float32) for x in n]
+        ntok = (C.c_int * len(clips))()
+        tk = C.c_int64(-1)
+        args = (B._ptr_array(clips), B._int_array(n), B._ptr_array(outs))
+        keep.append((args, ntok))                              # host arrays stay alive until the wait
+        B.check(enc.lib.q3a_encode_pcm_submit(fe.h, enc.h, args[0], args[1], len(clips), B.MODE_ASR, args[2], ntok, C.byref(tk)))
+        assert list(ntok) == [o.shape[0] for o in outs] and tk.value == (tickets[-1] + 1 if tickets else tk.value)
+        tickets.append(tk.value); outs_all.append(outs)
+        if k >= 1:
+            B.check(enc.lib.q3a_encode_wait(enc.h, tickets[k - 1]))
+            for a, b in zip(outs_all[k - 1], want[k - 1]):
+                assert np.array_equal(a, b)
+    B.check(enc.lib.q3a_encode_wait(enc.h, tickets[-1]))
+    for a, b in zip(outs_all[-1], want[-1]):
+        assert np.array_equal(a, b)
+    assert enc.lib.q3a_encode_wait(enc.h, tickets[-1] + 5) != 0
+    assert np.array_equal(enc.encode_pcm_batch(fe, batches[0], B.MODE_ASR)[1], want[0][1])     # the synchronous call still works after
+    enc.close(); fe.close()
