@@ -165,6 +165,13 @@ static int prof_collect(q3a_encoder* e, cudaStream_t st) {
     return Q3A_OK;
 }
 
+// Q3A_STEM_GROUP=<n>: run conv1 -> conv2 in groups of n chunks over a two-slot ring of plane rows (experiment; 0 = off)
+static int stem_group_chunks() {
+    const char* v = getenv("Q3A_STEM_GROUP");
+    const int g = v ? atoi(v) : 0;
+    return g > 0 ? g : 0;
+}
+
 // ---- the forward pass --------------------------------------------------------------------------------
 // Optional partition of one forward pass, used by the host-pointer entry points to overlap PCIe copies with
 // kernels.  Inputs: the stem runs part by part (utterances [in_split[i], in_split[i+1])), calling before_stem
@@ -351,28 +358,38 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         const int c0 = utt_chunk0[ua], nc = utt_chunk0[ub] - c0;
         const int t0 = (int)tok_off[ua], tn = (int)(tok_off[ub] - tok_off[ua]);
         if (nc == 0) continue;
-        const int row1 = c0 * P2, row2 = c0 * P3;          // first plane rows of the part
-        {
-            const int sp = prof.begin(SP_OTHER);
-            if (e->conv1_wimg)
-                Q3A_TRY(conv1_tc_launch<OpT>(mel_dev, d_chunks + c0, nc, P2, max_dev, e->conv1_wimg, e->conv1_b, C, planes1,
-                                             e->rcap1, row1, st));
-            else
-                Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks + c0, nc, P2, max_dev, e->conv1_w, e->conv1_b, C,
-                                          planes1 + (size_t)row1 * F2 * C, ps1, st));
-            prof.end(sp);
-        }
-        {
-            ConvArgs a;
-            a.planes = planes1 + (size_t)row1 * F2 * C; a.R_cap = e->rcap1; a.R_map = e->rcap1 - row1; a.R_used = nc * P2;
-            a.Fh = F2; a.C = C;
-            a.w = e->conv2_w; a.N = C; a.bias = e->conv2_b; a.P = P2;
-            a.out_planes = planes2 + (size_t)row2 * F3 * C; a.P_next = P3; a.out_plane_stride = ps2; a.ot_valid = d_t2 + c0;
-            const int sp = prof.begin(SP_GEMM);
-            Q3A_TRY(gemm_conv(false, fmt, a, st));
-            prof.end(sp);
-            double m = 0; for (int c = c0; c < c0 + nc; ++c) m += (double)t2_valid[c] * F2;
-            e->tm.gemm_flops += 2.0 * m * C * 9.0 * C; ++e->tm.gemm_launches;
+        const int row2 = c0 * P3;                           // first planes2 row of the part
+        // conv1 -> conv2.  Default: the whole part at once (planes1 rows = chunk * P2).  Experiment of VERDICT r1 item 4
+        // (Q3A_STEM_GROUP=<chunks>): groups of that many chunks over a two-slot ring of plane rows, so that the planes
+        // conv2 reads were written a moment ago and the ring (2 * G * 3.07 MB at C = 480) can stay dirty in the 126 MB
+        // L2 instead of travelling to HBM and back.  Results are identical either way (same kernels, same rows).
+        const int G = stem_group_chunks() > 0 ? stem_group_chunks() : nc;
+        int gi = 0;
+        for (int cg = c0; cg < c0 + nc; cg += G, ++gi) {
+            const int ncg = std::min(G, c0 + nc - cg);
+            const int row1 = stem_group_chunks() > 0 ? (gi & 1) * G * P2 : cg * P2;
+            {
+                const int sp = prof.begin(SP_OTHER);
+                if (e->conv1_wimg)
+                    Q3A_TRY(conv1_tc_launch<OpT>(mel_dev, d_chunks + cg, ncg, P2, max_dev, e->conv1_wimg, e->conv1_b, C, planes1,
+                                                 e->rcap1, row1, st));
+                else
+                    Q3A_TRY(conv1_launch<OpT>(mel_dev, d_chunks + cg, ncg, P2, max_dev, e->conv1_w, e->conv1_b, C,
+                                              planes1 + (size_t)row1 * F2 * C, ps1, st));
+                prof.end(sp);
+            }
+            {
+                ConvArgs a;
+                a.planes = planes1 + (size_t)row1 * F2 * C; a.R_cap = e->rcap1; a.R_map = e->rcap1 - row1; a.R_used = ncg * P2;
+                a.Fh = F2; a.C = C;
+                a.w = e->conv2_w; a.N = C; a.bias = e->conv2_b; a.P = P2;
+                a.out_planes = planes2 + (size_t)cg * P3 * F3 * C; a.P_next = P3; a.out_plane_stride = ps2; a.ot_valid = d_t2 + cg;
+                const int sp = prof.begin(SP_GEMM);
+                Q3A_TRY(gemm_conv(false, fmt, a, st));
+                prof.end(sp);
+                double m = 0; for (int c = cg; c < cg + ncg; ++c) m += (double)t2_valid[c] * F2;
+                e->tm.gemm_flops += 2.0 * m * C * 9.0 * C; ++e->tm.gemm_launches;
+            }
         }
         {
             ConvArgs a;
