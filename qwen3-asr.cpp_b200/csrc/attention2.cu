@@ -49,9 +49,10 @@ constexpr int kThreads = 384;
 constexpr int kTmemCols = 512;
 constexpr int kColS = 0, kColO = 256;       // S_X at kColS + 128 X, O_X at kColO + 64 X
 constexpr float kRescaleThreshold = 8.0f;   // log2 units: p <= 2^8 between rescales
-#ifndef Q3A_ATTN2_POLY
-#define Q3A_ATTN2_POLY 0                    // every n-th pair of exponentials on the FMA pipe (0 = all on MUFU)
-#endif
+// kPoly (template parameter): every kPoly-th pair of exponentials goes to the FMA pipe (ex2_poly) instead of MUFU; 0 = all
+// on MUFU.  The kernel is MUFU-bound once the chain is hidden (16 ex2/clk/SM), so moving a quarter to a third of them
+// to the 8 x wider FMA pipe raises the ceiling.  Q3A_ATTN2_POLY=<0|2|3|4> picks the instantiation (default below).
+constexpr int kDefaultPoly = 0;
 
 struct Smem {
     static constexpr int kQ = 0;                                    // 2 tiles
@@ -109,7 +110,7 @@ struct Geometry {                            // of one work item, derived identi
 
 }  // namespace
 
-template <class OpT>
+template <class OpT, int kPoly>
 __global__ void __launch_bounds__(kThreads, 1)
 attention2_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* __restrict__ items, int n_items, int n_heads,
                   OpT* __restrict__ out, int d_model) {
@@ -344,7 +345,7 @@ attention2_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttnTile* 
                                     const float a0 = fmaf(__uint_as_float(s[i + e]), kScale, neg_m);
                                     const float a1 = fmaf(__uint_as_float(s[i + e + 1]), kScale, neg_m);
                                     float p0, p1;
-                                    if (Q3A_ATTN2_POLY > 0 && ((i + e) / 2) % Q3A_ATTN2_POLY == Q3A_ATTN2_POLY - 1) {
+                                    if (kPoly > 0 && ((i + e) / 2) % (kPoly > 0 ? kPoly : 1) == kPoly - 1) {
                                         p0 = ex2_poly(a0); p1 = ex2_poly(a1);
                                     } else {
                                         p0 = tc::ex2_approx(a0); p1 = tc::ex2_approx(a1);
@@ -438,14 +439,12 @@ void attention2_items(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& i
     }
 }
 
-template <class OpT>
+template <class OpT, int kPoly>
 static int attention2_launch_t(const void* qkv, void* out, int T, int d, const AttnTile* items_dev, int n_items, int n_heads,
                                cudaStream_t stream) {
     CUtensorMap tm;
     Q3A_TRY(make_tmap_2d(&tm, qkv, (uint64_t)T, (uint64_t)3 * d, (uint64_t)3 * d, 128));
-    auto kern = attention2_kernel<OpT>;
-    int pairs_unused = 0;
-    (void)pairs_unused;
+    auto kern = attention2_kernel<OpT, kPoly>;
     Q3A_TRY(kernel_smem_optin(reinterpret_cast<const void*>(kern), Smem::kTotal));
     const long long units = (long long)n_items * n_heads;
     const int grid = (int)std::min<long long>(units, sm_count_cached());
@@ -459,8 +458,18 @@ int attention2_launch(const void* qkv, void* out, int T, int n_heads, const Attn
                       cudaStream_t stream) {
     if (n_items == 0 || T == 0) return Q3A_OK;
     const int d = n_heads * kHd;
-    if (fmt == OP_F16) return attention2_launch_t<__half>(qkv, out, T, d, items_dev, n_items, n_heads, stream);
-    return attention2_launch_t<__nv_bfloat16>(qkv, out, T, d, items_dev, n_items, n_heads, stream);
+    const char* pe = getenv("Q3A_ATTN2_POLY");
+    const int poly = pe ? atoi(pe) : kDefaultPoly;
+#define Q3A_A2(P)                                                                                                          \
+    return fmt == OP_F16 ? attention2_launch_t<__half, P>(qkv, out, T, d, items_dev, n_items, n_heads, stream)            \
+                         : attention2_launch_t<__nv_bfloat16, P>(qkv, out, T, d, items_dev, n_items, n_heads, stream)
+    switch (poly) {
+        case 2: Q3A_A2(2);
+        case 3: Q3A_A2(3);
+        case 4: Q3A_A2(4);
+        default: Q3A_A2(0);
+    }
+#undef Q3A_A2
 }
 
 }  // namespace q3a

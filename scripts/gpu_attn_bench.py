@@ -12,6 +12,7 @@ SHAPES = [(14, 390, 64), (14, 1196, 8), (16, 104, 480), (14, 4096, 4)]
 if os.environ.get("ATTN_L"):
     SHAPES = [(14, int(os.environ["ATTN_L"]), int(os.environ.get("ATTN_NS", 64)))]
 VERSIONS = [int(v) for v in os.environ.get("ATTN_V", "1,2").split(",")]
+POLYS = [int(v) for v in os.environ.get("ATTN_POLY", "0,4,3,2").split(",")]
 for H, L, NS in SHAPES:
     cu = [i * L for i in range(NS + 1)]
     T = cu[-1]
@@ -23,7 +24,8 @@ for H, L, NS in SHAPES:
     cu_arr = B._int_array(cu)
     st = torch.cuda.current_stream().cuda_stream
     flops = 4.0 * 64 * H * NS * L * L
-    for ver in VERSIONS:
+    for ver, poly in [(v, p) for v in VERSIONS for p in (POLYS if v == 2 else [0])]:
+        os.environ["Q3A_ATTN2_POLY"] = str(poly)
         out = torch.zeros(T, H * 64, device="cuda", dtype=torch.bfloat16)
         times = []
         for it in range(12):
@@ -34,5 +36,5 @@ for H, L, NS in SHAPES:
             times.append(e0.elapsed_time(e1) * 1e3)
         best = min(times[2:])
         err = (out[s].float() - want).abs().max().item()
-        print(f"attention v{ver} {NS}x{L} H={H}: best {best:.1f} us ({flops / best / 1e6:.0f} TFLOP/s), last-seg max err {err:.4f}, "
+        print(f"attention v{ver} poly={poly} {NS}x{L} H={H}: best {best:.1f} us ({flops / best / 1e6:.0f} TFLOP/s), last-seg max err {err:.4f}, "
               f"all {[round(t) for t in times]}", flush=True)
