@@ -1,0 +1,18 @@
+#!/bin/bash
+# round 2, visit B: full GPU test suite, smoke, both bench arms, then the ncu evidence (launch list with DRAM bytes of one
+# bench step; --set full captures of the attention and GEMM kernels).  ncu only after the same command exited 0 plain.
+set -u
+mkdir -p gpurun_out
+timeout 2400 python -m pytest tests -x -q -m gpu > gpurun_out/r2b_pytest.log 2>&1; echo "pytest exit=$?" | tee -a gpurun_out/r2b_pytest.log; tail -4 gpurun_out/r2b_pytest.log
+timeout 300 python __graft_entry__.py --smoke > gpurun_out/r2b_smoke.log 2>&1; echo "smoke exit=$?"; tail -3 gpurun_out/r2b_smoke.log
+timeout 900 python bench.py > gpurun_out/r2b_bench.json 2> gpurun_out/r2b_bench.err; echo "bench exit=$?"; cat gpurun_out/r2b_bench.json
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2b_bench_ref.json 2> gpurun_out/r2b_bench_ref.err; echo "bench ref exit=$?"; cat gpurun_out/r2b_bench_ref.json
+python qwen3-asr.cpp_b200/build.py --hash > gpurun_out/csrc_sha256.txt
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-corpus"
+timeout 300 $CMD > gpurun_out/plain.log 2>&1 &&
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --print-units base --clock-control none -k regex:'q3a|mel|conv1|attention|gemm|layernorm|pcm16' -c 2000 --csv --log-file gpurun_out/launches_all.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+echo "ncu launches exit=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:attention2 -s 40 -c 2 -f -o gpurun_out/prof_attn2 $CMD > gpurun_out/ncu_attn.log 2>&1; echo "ncu attn exit=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_tc -s 300 -c 8 -f -o gpurun_out/prof_gemm $CMD > gpurun_out/ncu_gemm.log 2>&1; echo "ncu gemm exit=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:mel_frames -s 3 -c 1 -f -o gpurun_out/prof_mel $CMD > gpurun_out/ncu_mel.log 2>&1; echo "ncu mel exit=$?"
+ls -la gpurun_out | tail -20
