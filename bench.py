@@ -354,7 +354,10 @@ def run_ours(args):
     T = enc.n_tokens(n // 160) * BATCH
     out_dev = torch.empty((T, enc.hp.out_dim), dtype=torch.float32, device="cuda")
     # two sets of pinned feature buffers: the asynchronous call keeps two steps in flight
-    out_hosts = [[torch.empty((T // BATCH, enc.hp.out_dim), dtype=torch.float32).pin_memory() for _ in range(BATCH)] for _ in range(2)]
+    # (each set is one pinned block, a clip's rows at its offset: the library then moves a download part with one copy)
+    out_blocks = [torch.empty((T, enc.hp.out_dim), dtype=torch.float32).pin_memory() for _ in range(2)]
+    rows_per_clip = T // BATCH
+    out_hosts = [[blk[i * rows_per_clip:(i + 1) * rows_per_clip] for i in range(BATCH)] for blk in out_blocks]
     out_host = out_hosts[0]
     stream = torch.cuda.current_stream().cuda_stream
 
@@ -446,7 +449,7 @@ def run_ours(args):
     step_dev(0)
     torch.cuda.synchronize()
     got = out_dev.cpu()
-    want = torch.cat(out_host, dim=0)
+    want = out_blocks[0]
     finite = bool(torch.isfinite(got).all())
     max_diff = float((got - want).abs().max()) if finite else float("nan")
     ok = torch.tensor([1 if (finite and torch.equal(got, want)) else 0], device="cuda")

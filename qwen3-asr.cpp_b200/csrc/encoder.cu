@@ -958,10 +958,22 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
         if (g0 + p >= 2) PIPE_CUDA(cudaStreamWaitEvent(e->copy_in, e->ev_comp[b], 0));   // pass g-2 (maybe of an earlier call) has consumed the buffer
         const std::vector<int>& sp = in_split[p];
         for (size_t part = 0; part + 1 < sp.size(); ++part) {
-            for (int i = sp[part]; i < sp[part + 1]; ++i)
-                if (in_elems[u0 + i] > 0)
-                    PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<uint8_t>() + (size_t)elem_bytes * ioff[p][i], in[u0 + i],
-                                              (size_t)elem_bytes * in_elems[u0 + i], cudaMemcpyHostToDevice, e->copy_in));
+            // one copy per run of clips that are contiguous on both sides (a caller that keeps its clips in one pinned
+            // block gets one transfer per part instead of one per clip)
+            for (int i = sp[part]; i < sp[part + 1];) {
+                if (in_elems[u0 + i] <= 0) { ++i; continue; }
+                const uint8_t* src = static_cast<const uint8_t*>(in[u0 + i]);
+                const size_t dst0 = (size_t)elem_bytes * ioff[p][i];
+                size_t bytes = (size_t)elem_bytes * in_elems[u0 + i];
+                int j = i + 1;
+                while (j < sp[part + 1] && in_elems[u0 + j] > 0 && static_cast<const uint8_t*>(in[u0 + j]) == src + bytes &&
+                       (size_t)elem_bytes * ioff[p][j] == dst0 + bytes) {
+                    bytes += (size_t)elem_bytes * in_elems[u0 + j];
+                    ++j;
+                }
+                PIPE_CUDA(cudaMemcpyAsync(sin[b]->as<uint8_t>() + dst0, src, bytes, cudaMemcpyHostToDevice, e->copy_in));
+                i = j;
+            }
             PIPE_CUDA(cudaEventRecord(e->ev_part_in[b][part], e->copy_in));
         }
         return Q3A_OK;
@@ -985,12 +997,18 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
         hk.after_out = [&, b, u0](int part, int ua, int ub, const int64_t* toff) -> int {
             HOOK_CUDA(cudaEventRecord(e->ev_part_out[b][part], e->stream));
             HOOK_CUDA(cudaStreamWaitEvent(e->copy_out, e->ev_part_out[b][part], 0));
-            for (int i = ua; i < ub; ++i) {
+            for (int i = ua; i < ub; ++i)
+                if (n_tokens) n_tokens[u0 + i] = (int)(toff[i + 1] - toff[i]);
+            for (int i = ua; i < ub;) {                       // rows are consecutive on the device: merge contiguous host targets
                 const int64_t rows = toff[i + 1] - toff[i];
-                if (n_tokens) n_tokens[u0 + i] = (int)rows;
-                if (rows > 0)
-                    HOOK_CUDA(cudaMemcpyAsync(out[u0 + i], sout[b]->as<float>() + toff[i] * width, sizeof(float) * rows * width,
-                                              cudaMemcpyDeviceToHost, e->copy_out));
+                if (rows <= 0) { ++i; continue; }
+                float* dst = out[u0 + i];
+                int64_t total = rows;
+                int j = i + 1;
+                while (j < ub && (toff[j + 1] - toff[j] <= 0 || out[u0 + j] == dst + total * width)) { total += toff[j + 1] - toff[j]; ++j; }
+                HOOK_CUDA(cudaMemcpyAsync(dst, sout[b]->as<float>() + toff[i] * width, sizeof(float) * total * width,
+                                          cudaMemcpyDeviceToHost, e->copy_out));
+                i = j;
             }
             return Q3A_OK;
         };

@@ -531,3 +531,29 @@ def test_async_submit_wait_matches_synchronous_call(lib, asr_model):
     assert enc.lib.q3a_encode_wait(enc.h, tickets[-1] + 5) != 0
     assert np.array_equal(enc.encode_pcm_batch(fe, batches[0], B.MODE_ASR)[1], want[0][1])     # the synchronous call still works after
     enc.close(); fe.close()
+
+
+def test_contiguous_host_blocks_take_the_merged_copy_path(lib, tiny_models):
+    """Clips that sit back to back in one host block (lengths multiples of 64 samples) and feature buffers that sit back
+    to back in another are moved with one copy per run instead of one per clip; the features must not change."""
+    import ctypes as C
+    shape, models = tiny_models
+    enc = B.Encoder(models["f16"][0], 0, B.OP_F16)
+    fe = B.Frontend(0)
+    lens = [64 * 700, 64 * 130, 0, 64 * 999, 64 * 250 + 17, 64 * 40]        # one empty clip, one that breaks the run
+    src = [synth.synth_audio(1300 + i, n) for i, n in enumerate(lens)]
+    want = enc.encode_pcm_batch(fe, src, B.MODE_ASR)
+    block = np.concatenate(src).astype(np.float32)
+    offs = np.cumsum([0] + lens)
+    clips = [block[offs[i]:offs[i + 1]] for i in range(len(lens))]
+    toks = [w.shape[0] for w in want]
+    toff = np.cumsum([0] + toks)
+    out_block = np.full((toff[-1], shape.out_dim), np.nan, np.float32)
+    outs = [out_block[toff[i]:toff[i + 1]] for i in range(len(lens))]
+    ntok = (C.c_int * len(lens))()
+    B.check(enc.lib.q3a_encode_pcm_batch(fe.h, enc.h, B._ptr_array(clips), B._int_array(lens), len(lens), B.MODE_ASR,
+                                         B._ptr_array(outs), ntok))
+    assert list(ntok) == toks
+    for a, b in zip(outs, want):
+        assert np.array_equal(a, b)
+    enc.close(); fe.close()
