@@ -182,6 +182,27 @@ int q3a_encoder_get_timings(const q3a_encoder* enc, q3a_timings* out);
 /* bytes of device memory held by the encoder (weights + workspace) */
 int64_t q3a_encoder_device_bytes(const q3a_encoder* enc);
 
+/* ---- forced aligner: NAR decoder prefill (csrc/decoder.cu) ------------------------------------------------------------
+ * replaces ForcedAligner::forward_decoder / build_decoder_graph (forced_aligner.cpp:926-1169): one causal forward over the
+ * prompt -- token embeddings with the audio features spliced in at [audio_start, audio_start + n_audio) -- through the
+ * Qwen3 decoder layers and the classification head: logits [n_tokens][n_classes] f32 row-major, the memory
+ * extract_timestamp_classes (forced_aligner.cpp:1279-1308) reads.  Weights: token_embd / blk.N.* / output_norm / output of
+ * the same GGUF the aligner's encoder is loaded from (hyper-parameter keys of parse_hparams, :158-168).  head_dim must
+ * be 128.  The _device variant takes the audio features where q3a_encode_pcm_device left them (device memory, f32
+ * [n_audio][hidden]) and leaves the logits on the device, asynchronously on `stream`; tokens are host memory. */
+typedef struct q3a_decoder q3a_decoder;
+typedef struct q3a_decoder_hparams {
+    int32_t n_layers, hidden, n_heads, n_kv_heads, head_dim, intermediate, vocab, n_classes;
+    float rms_eps, rope_theta;
+} q3a_decoder_hparams;
+int q3a_decoder_load(const char* gguf_path, int device, int operand_dtype, q3a_decoder** out);
+void q3a_decoder_free(q3a_decoder* dec);
+int q3a_decoder_get_hparams(const q3a_decoder* dec, q3a_decoder_hparams* out);
+int q3a_decoder_forward(q3a_decoder* dec, const int32_t* tokens, int n_tokens, const float* audio_embd, int n_audio,
+                        int audio_start, float* logits);
+int q3a_decoder_forward_device(q3a_decoder* dec, const int32_t* tokens, int n_tokens, const float* audio_dev, int n_audio,
+                               int audio_start, float* logits_dev, void* stream);
+
 /* ---- utterance sharding (no collective on the compute path) ------------------------------ */
 
 /* Longest-processing-time assignment of utterances to n_shards replicas by predicted cost

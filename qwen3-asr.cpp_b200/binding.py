@@ -65,6 +65,11 @@ SYMBOLS = {
     "q3a_encoder_set_profiling": (_I, [_P, _I]),
     "q3a_encoder_get_timings": (_I, [_P, C.POINTER(Timings)]),
     "q3a_encoder_device_bytes": (_I64, [_P]),
+    "q3a_decoder_load": (_I, [C.c_char_p, _I, _I, C.POINTER(_P)]),
+    "q3a_decoder_free": (None, [_P]),
+    "q3a_decoder_get_hparams": (_I, [_P, _P]),
+    "q3a_decoder_forward": (_I, [_P, _P, _I, _P, _I, _I, _P]),
+    "q3a_decoder_forward_device": (_I, [_P, _P, _I, _P, _I, _I, _P, _P]),
     "q3a_plan_shards": (_I, [_P, _I, _I, _I, _P]),
     "q3a_pool_create": (_I, [C.c_char_p, _P, _I, _I, C.POINTER(_P)]),
     "q3a_pool_free": (None, [_P]),
@@ -255,6 +260,47 @@ class Encoder:
 
     def device_bytes(self) -> int:
         return int(self.lib.q3a_encoder_device_bytes(self.h))
+
+
+class DecoderHParams(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("n_layers", "hidden", "n_heads", "n_kv_heads", "head_dim", "intermediate", "vocab",
+                                         "n_classes")] + [("rms_eps", C.c_float), ("rope_theta", C.c_float)]
+
+
+class Decoder:
+    """q3a_decoder: the forced aligner's NAR decoder (prefill over the whole prompt, classification head)."""
+
+    def __init__(self, gguf_path: str, device: int = 0, operand: int = OP_BF16):
+        self.lib = load()
+        self.h = C.c_void_p()
+        check(self.lib.q3a_decoder_load(gguf_path.encode(), device, operand, C.byref(self.h)))
+        self.hp = DecoderHParams()
+        check(self.lib.q3a_decoder_get_hparams(self.h, C.byref(self.hp)))
+
+    def close(self):
+        if self.h:
+            self.lib.q3a_decoder_free(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def forward(self, tokens, audio: np.ndarray | None = None, audio_start: int = -1) -> np.ndarray:
+        tok = np.ascontiguousarray(tokens, dtype=np.int32)
+        out = np.zeros((len(tok), self.hp.n_classes), dtype=np.float32)
+        if audio is not None:
+            audio = np.ascontiguousarray(audio, dtype=np.float32)
+        check(self.lib.q3a_decoder_forward(self.h, tok.ctypes.data, len(tok), audio.ctypes.data if audio is not None else None,
+                                           len(audio) if audio is not None else 0, audio_start, out.ctypes.data))
+        return out
+
+    def forward_device(self, tokens, audio_ptr: int, n_audio: int, audio_start: int, logits_ptr: int, stream: int = 0) -> None:
+        tok = np.ascontiguousarray(tokens, dtype=np.int32)
+        check(self.lib.q3a_decoder_forward_device(self.h, tok.ctypes.data, len(tok), audio_ptr or None, n_audio, audio_start,
+                                                  logits_ptr, stream or None))
 
 
 class Pool:

@@ -145,6 +145,16 @@ template <class OpT> struct EpiDual<EpiPosEmbF32Dual<OpT>> { static constexpr bo
 
 // consumer side: 16-bit out = act(rstd * (acc - mean * s[n]) + c[n])
 struct LnRowState { float mean, rstd; };
+__device__ __forceinline__ LnRowState ln_row_state(const float2* stats, int n_part, int M, float inv_d, float eps, int rms, int m) {
+    float sum = 0.0f, sq = 0.0f;
+    if (m < M) {
+        const float2* p = stats + (size_t)m * n_part;
+        for (int i = 0; i < n_part; ++i) { const float2 t = __ldg(p + i); sum += t.x; sq += t.y; }
+    }
+    const float mean = rms ? 0.0f : sum * inv_d;
+    const float var = fmaxf(sq * inv_d - mean * mean, 0.0f);
+    return LnRowState{mean, 1.0f / sqrtf(var + eps)};
+}
 template <class OpT, bool kGelu>
 struct EpiLnFoldActOp {
     static constexpr bool kStaged = true, kResidual = false;
@@ -155,17 +165,9 @@ struct EpiLnFoldActOp {
     const float2* stats;     // [M][n_part]
     int n_part, M;
     float inv_d, eps;
+    int rms;                 // 1: RMSNorm (no mean subtraction; the aligner's decoder, forced_aligner.cpp:1012-1013)
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
-    __device__ __forceinline__ RowState row_state(int m) const {
-        float sum = 0.0f, sq = 0.0f;
-        if (m < M) {
-            const float2* p = stats + (size_t)m * n_part;
-            for (int i = 0; i < n_part; ++i) { const float2 t = __ldg(p + i); sum += t.x; sq += t.y; }
-        }
-        const float mean = sum * inv_d;
-        const float var = fmaxf(sq * inv_d - mean * mean, 0.0f);
-        return RowState{mean, 1.0f / sqrtf(var + eps)};
-    }
+    __device__ __forceinline__ RowState row_state(int m) const { return ln_row_state(stats, n_part, M, inv_d, eps, rms, m); }
     __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32], const RowState& rs) const {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -178,6 +180,30 @@ struct EpiLnFoldActOp {
                     const float x = fmaf(rs.rstd, fmaf(-rs.mean, ss[j], v[g * 8 + j]), cc[j]);
                     v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
                 }
+            }
+        }
+    }
+};
+
+// same fold, f32 output (the decoder's classification head: logits = rmsnorm(x) W^T + b, forced_aligner.cpp:1070-1076)
+struct EpiLnFoldF32 {
+    static constexpr bool kStaged = true, kResidual = false;
+    static constexpr int kOutBytes = 4;
+    using RowState = LnRowState;
+    const float* c; const float* s; const float2* stats;
+    int n_part, M;
+    float inv_d, eps;
+    int rms;
+    __device__ __forceinline__ RowState row_state(int m) const { return ln_row_state(stats, n_part, M, inv_d, eps, rms, m); }
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32], const RowState& rs) const {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float cc[8], ss[8];
+                load8(c + n0 + g * 8, cc);
+                load8(s + n0 + g * 8, ss);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] = fmaf(rs.rstd, fmaf(-rs.mean, ss[j], v[g * 8 + j]), cc[j]);
             }
         }
     }

@@ -16,6 +16,7 @@ enum EpiKind : int {
     EPI_POSEMB_F32_DUAL = 6,     // f32 out = acc + pe[pos[m]] ; out16 ; stats
     EPI_LNFOLD_OP = 7,           // 16-bit out = rstd * (acc - mean * colsum) + bias'
     EPI_LNFOLD_GELU_OP = 8,      // 16-bit out = gelu(...)
+    EPI_LNFOLD_F32 = 9,          // f32 out = rstd * (acc - mean * colsum) + bias'
 };
 
 struct LinearArgs {
@@ -37,6 +38,7 @@ struct LinearArgs {
     int n_part = 0;            // partials per row = 2 * ceil(d_model / BLOCK_N of the producer): ln_partials()
     const float* colsum = nullptr;   // LNFOLD: [N]
     float ln_inv_d = 0.0f, ln_eps = 0.0f;
+    int ln_rms = 0;            // LNFOLD: RMSNorm instead of LayerNorm (no mean)
 };
 // statistics partials per row that a DUAL GEMM with N output columns writes
 int ln_partials(int N);

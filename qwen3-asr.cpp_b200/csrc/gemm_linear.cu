@@ -142,8 +142,11 @@ static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) 
         case EPI_LNFOLD_GELU_OP:
             if (!a.bias || !a.colsum || !a.stats || a.n_part <= 0) { set_error("gemm_linear: LayerNorm fold needs bias', colsum and stats"); return Q3A_ERR_ARG; }
             if (kind == EPI_LNFOLD_OP)
-                return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldActOp<OpT, false>{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps}, stream);
-            return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldActOp<OpT, true>{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps}, stream);
+                return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldActOp<OpT, false>{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps, a.ln_rms}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldActOp<OpT, true>{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps, a.ln_rms}, stream);
+        case EPI_LNFOLD_F32:
+            if (!a.bias || !a.colsum || !a.stats || a.n_part <= 0) { set_error("gemm_linear: LayerNorm fold needs bias', colsum and stats"); return Q3A_ERR_ARG; }
+            return launch_linear<BLOCK_N, kFmt>(a, EpiLnFoldF32{a.bias, a.colsum, a.stats, a.n_part, a.M, a.ln_inv_d, a.ln_eps, a.ln_rms}, stream);
     }
     set_error("gemm_linear: unknown epilogue");
     return Q3A_ERR_ARG;

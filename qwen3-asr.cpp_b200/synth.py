@@ -179,3 +179,88 @@ def chunk_tokens(n_frames: int) -> int:
 def mel_frames(n_samples: int) -> int:
     """n_len of log_mel_spectrogram (mel_spectrogram.cpp:517-520)."""
     return n_samples // 160
+
+
+# ---- forced aligner: NAR decoder (forced_aligner.h:50-61; tensor names forced_aligner.cpp:267-314,381-410) -----------
+@dataclass(frozen=True)
+class DecoderShape:
+    name: str
+    n_layers: int
+    hidden: int
+    n_heads: int
+    n_kv_heads: int
+    intermediate: int
+    vocab: int
+    n_classes: int
+    head_dim: int = 128
+    rms_eps: float = 1e-6
+    rope_theta: float = 1000000.0
+
+
+ALIGNER_DECODER_06B = DecoderShape("qwen3-forced-aligner-0.6b-decoder", 28, 1024, 16, 8, 3072, 152064, 5000)
+
+
+def tiny_decoder_shape() -> DecoderShape:
+    """Same topology (head_dim 128, 2 query heads per kv head), small enough for a CPU oracle in milliseconds."""
+    return DecoderShape("tiny-decoder", 3, 128, 4, 2, 256, 320, 48)
+
+
+def random_decoder_weights(shape: DecoderShape, seed: int) -> dict[str, np.ndarray]:
+    rng = np.random.default_rng(seed)
+    w: dict[str, np.ndarray] = {}
+
+    def lin(name, n_out, n_in):
+        w[name] = (rng.standard_normal((n_out, n_in)) / np.sqrt(n_in)).astype(np.float32)
+
+    def norm(name, n):
+        w[name] = (1.0 + rng.standard_normal(n) * 0.05).astype(np.float32)
+
+    dq, dkv = shape.n_heads * shape.head_dim, shape.n_kv_heads * shape.head_dim
+    w["token_embd.weight"] = (rng.standard_normal((shape.vocab, shape.hidden)) * 0.5).astype(np.float32)
+    for l in range(shape.n_layers):
+        p = f"blk.{l}"
+        norm(f"{p}.attn_norm.weight", shape.hidden)
+        lin(f"{p}.attn_q.weight", dq, shape.hidden)
+        lin(f"{p}.attn_k.weight", dkv, shape.hidden)
+        lin(f"{p}.attn_v.weight", dkv, shape.hidden)
+        norm(f"{p}.attn_q_norm.weight", shape.head_dim)
+        norm(f"{p}.attn_k_norm.weight", shape.head_dim)
+        lin(f"{p}.attn_output.weight", shape.hidden, dq)
+        norm(f"{p}.ffn_norm.weight", shape.hidden)
+        lin(f"{p}.ffn_gate.weight", shape.intermediate, shape.hidden)
+        lin(f"{p}.ffn_up.weight", shape.intermediate, shape.hidden)
+        lin(f"{p}.ffn_down.weight", shape.hidden, shape.intermediate)
+    norm("output_norm.weight", shape.hidden)
+    lin("output.weight", shape.n_classes, shape.hidden)
+    return w
+
+
+def write_decoder_gguf(path: str, shape: DecoderShape, weights: dict[str, np.ndarray], ftype: str = "f16") -> str:
+    """The decoder half of an aligner GGUF: the keys ForcedAligner::parse_hparams reads (forced_aligner.cpp:158-168)."""
+    import gguf
+    from gguf import GGMLQuantizationType as QT
+    assert ftype in ("f32", "f16")
+    os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+    wr = gguf.GGUFWriter(path, "qwen3-asr")
+    wr.add_name(shape.name)
+    a = "qwen3-asr"
+    wr.add_uint32(f"{a}.block_count", shape.n_layers)
+    wr.add_uint32(f"{a}.embedding_length", shape.hidden)
+    wr.add_uint32(f"{a}.attention.head_count", shape.n_heads)
+    wr.add_uint32(f"{a}.attention.head_count_kv", shape.n_kv_heads)
+    wr.add_uint32(f"{a}.feed_forward_length", shape.intermediate)
+    wr.add_uint32(f"{a}.attention.key_length", shape.head_dim)
+    wr.add_float32(f"{a}.attention.layer_norm_rms_epsilon", shape.rms_eps)
+    wr.add_float32(f"{a}.rope.freq_base", shape.rope_theta)
+    wr.add_uint32(f"{a}.vocab_size", shape.vocab)
+    wr.add_uint32(f"{a}.classify_num", shape.n_classes)
+    for name, t in weights.items():
+        if t.ndim <= 1 or ftype == "f32":
+            wr.add_tensor(name, np.ascontiguousarray(t, dtype=np.float32), raw_dtype=QT.F32)
+        else:
+            wr.add_tensor(name, np.ascontiguousarray(t.astype(np.float16)), raw_dtype=QT.F16)
+    wr.write_header_to_file()
+    wr.write_kv_data_to_file()
+    wr.write_tensors_to_file()
+    wr.close()
+    return path
