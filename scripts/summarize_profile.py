@@ -44,6 +44,9 @@ def launches(tag: str) -> None:
     """gpurun_out/launches.csv: one ncu pass over the launches of ONE bench step with
     --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --print-units base."""
     path = os.path.join(GO, "launches.csv")
+    whole_run = os.path.join(GO, "launches_all.csv")       # every launch of the run: one device-resident step is cut out below
+    if os.path.exists(whole_run):
+        path = whole_run
     if not os.path.exists(path):
         return
     rows = list(csv.reader(open(path, newline="")))
@@ -60,6 +63,14 @@ def launches(tag: str) -> None:
             d[r[mn]] = float(r[mv].replace(",", ""))
         except ValueError:
             pass
+    if path == whole_run:
+        # a device-resident step starts with its single mel_frames_kernel launch: keep [2nd such launch, 3rd) -- past the
+        # first (cold) step, before the host-pointer steps (which launch the mel kernel once per upload part)
+        ids = list(per_launch)
+        starts = [i for i, k in enumerate(ids) if per_launch[k]["key"][0].startswith("mel_frames_kernel")]
+        if len(starts) >= 3:
+            keep = ids[starts[1]:starts[2]]
+            per_launch = collections.OrderedDict((k, per_launch[k]) for k in keep)
     agg: dict = collections.OrderedDict()
     total = 0.0
     for d in per_launch.values():
@@ -132,7 +143,7 @@ def full_reports(tag: str) -> None:
 
 
 def bench(tag: str) -> None:
-    for name in ("bench.json", "bench_ref.json"):
+    for name in ("bench.json", "bench_ref.json", "r2b_bench.json", "r2b_bench_ref.json"):
         p = os.path.join(GO, name)
         if os.path.exists(p) and os.path.getsize(p) > 0:
             with open(p) as f:
