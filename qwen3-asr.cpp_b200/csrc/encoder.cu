@@ -238,6 +238,13 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     // ---- workspace ----------------------------------------------------------------------------------------
     if (mode != Q3A_MODE_CONV_ONLY) Q3A_TRY(ensure_pe(e, max_pos, st));
     const int r1 = n_chunks * P2, r2 = n_chunks * P3;
+    // Every chunk of a pass owns P2 plane rows, P2 taken from the longest one.  The chunked modes bound that at 100 frames;
+    // the debug modes (one chunk = one utterance) do not, so a ragged batch there can ask for n_utts * max_len rows.
+    if ((double)r1 * F2 * C * 2.0 * 4.0 > 48e9) {
+        set_error("encode: the stem workspace of this batch would exceed 48 GB (no-chunk / conv-only modes size every utterance's "
+                  "planes by the longest one): split the batch by length");
+        return Q3A_ERR_ARG;
+    }
     if (r1 > e->rcap1 || P2 != e->sigP2) {
         const int cap = std::max(r1 + r1 / 4, e->rcap1);
         Q3A_CUDA(cudaStreamSynchronize(st));
