@@ -133,3 +133,49 @@ def test_host_binding_never_raises_and_never_widens():
     assert info["bound"] == (after != before)
     assert info["cpus"] == len(after)
     os.sched_setaffinity(0, before)
+
+
+def test_round2_entry_points_validate_their_arguments(lib, tmp_path):
+    """pool, asynchronous call, decoder and host helpers: argument and state errors are reported before any CUDA work, so
+    they behave the same on a box without a GPU."""
+    h = C.c_void_p()
+    devs = (C.c_int * 2)(0, 0)
+    assert lib.q3a_pool_create(None, devs, 2, B.OP_BF16, C.byref(h)) == 1 and not h.value            # Q3A_ERR_ARG
+    assert lib.q3a_pool_create(b"x.gguf", devs, 0, B.OP_BF16, C.byref(h)) == 1
+    assert lib.q3a_pool_create(b"x.gguf", devs, 2, B.OP_BF16, None) == 1
+    assert lib.q3a_pool_n_devices(None) == 0
+    assert lib.q3a_pool_encode_pcm(None, None, None, 0, 0, None, None, None, None) == 5              # Q3A_ERR_STATE
+    lib.q3a_pool_free(None)
+    tk = C.c_int64(-1)
+    assert lib.q3a_encode_pcm_submit(None, None, None, None, 0, 0, None, None, C.byref(tk)) == 5
+    assert lib.q3a_encode_wait(None, 0) == 5
+    rc = lib.q3a_decoder_load(str(tmp_path / "missing.gguf").encode(), 0, B.OP_BF16, C.byref(h))
+    assert rc == 3 and b"cannot open" in lib.q3a_last_error()                                         # Q3A_ERR_IO
+    assert lib.q3a_decoder_load(None, 0, B.OP_BF16, C.byref(h)) == 1
+    assert lib.q3a_decoder_load(b"x.gguf", 0, 9, C.byref(h)) == 1
+    assert lib.q3a_decoder_forward(None, None, 0, None, 0, -1, None) == 5
+    assert lib.q3a_decoder_get_hparams(None, None) == 5
+    lib.q3a_decoder_free(None)
+    p = C.c_void_p(1)
+    assert lib.q3a_host_alloc(0, C.byref(p)) == 0 and not p.value                                      # zero bytes: OK, null
+    assert lib.q3a_host_alloc(16, None) == 1
+    lib.q3a_host_free(None)
+    # an encoder-only GGUF is not an aligner decoder file
+    shape = synth.tiny_shape()
+    path = synth.write_gguf(str(tmp_path / "enc.gguf"), shape, synth.random_weights(shape, 7), "f16")
+    rc = lib.q3a_decoder_load(path.encode(), 0, B.OP_BF16, C.byref(h))
+    assert rc in (2, 4) and not h.value        # FORMAT on a GPU box; no device is reported first where there is none
+
+
+def test_decoder_gguf_round_trip_keys(lib, tmp_path):
+    """the decoder GGUF the tests write carries the keys ForcedAligner::parse_hparams reads (forced_aligner.cpp:158-168)"""
+    import gguf
+    shape = synth.tiny_decoder_shape()
+    path = synth.write_decoder_gguf(str(tmp_path / "dec.gguf"), shape, synth.random_decoder_weights(shape, 3), "f16")
+    r = gguf.GGUFReader(path)
+    keys = set(r.fields)
+    for k in ("block_count", "embedding_length", "attention.head_count", "attention.head_count_kv", "feed_forward_length",
+              "attention.key_length", "attention.layer_norm_rms_epsilon", "rope.freq_base", "vocab_size", "classify_num"):
+        assert f"qwen3-asr.{k}" in keys
+    names = {t.name for t in r.tensors}
+    assert {"token_embd.weight", "output_norm.weight", "output.weight", "blk.0.attn_q_norm.weight", "blk.2.ffn_gate.weight"} <= names
