@@ -67,11 +67,14 @@ template <> struct OpTraits<__half> {
 // ggml_gelu is the tanh form (audio_encoder.cpp:112 -> ggml_gelu); MUFU.TANH is accurate to
 // ~2^-11 relative, the same order as the f16 table ggml's CPU path reads it through.
 __device__ __forceinline__ float gelu_tanh(float x) {
-    const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-    float u = k0 * x * fmaf(k1 * x, x, 1.0f);
+    // 5 FP32 instructions + one MUFU (the epilogues of the FFN-up GEMM and of the conv stem are issue-bound on this):
+    // u = x (k0 + k0 k1 x^2), y = x/2 + x/2 tanh(u)
+    const float k0 = 0.7978845608028654f, k0k1 = 0.7978845608028654f * 0.044715f;
+    const float u = x * fmaf(k0k1, x * x, k0);
     float t;
     asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
-    return 0.5f * x * (1.0f + t);
+    const float hx = 0.5f * x;
+    return fmaf(hx, t, hx);
 }
 
 __host__ __device__ constexpr int ceil_div(int a, int b) { return (a + b - 1) / b; }
