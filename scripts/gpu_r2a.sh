@@ -24,11 +24,12 @@ TAIL=8 run decoder_pytest timeout 600 $PT tests/test_decoder_gpu.py
 run bench timeout 900 python bench.py --steps 10 --warmup 3; cat gpurun_out/r2a_bench.log | head -c 6000
 Q3A_NO_LN_FOLD=1 run bench_nofold timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
 Q3A_ATTN_V1=1 run bench_attnv1 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
+Q3A_CONV_TAP_MAJOR=1 run bench_tapmajor timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
 Q3A_STEM_GROUP=11 run bench_group11 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
 Q3A_STEM_GROUP=22 run bench_group22 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
 python - <<'PY'
 import json
-for n in ("bench", "bench_nofold", "bench_attnv1", "bench_group11", "bench_group22"):
+for n in ("bench", "bench_nofold", "bench_attnv1", "bench_tapmajor", "bench_group11", "bench_group22"):
     try:
         line = [l for l in open(f"gpurun_out/r2a_{n}.log") if l.startswith("{")][-1]
         d = json.loads(line)
