@@ -7,6 +7,7 @@
 #include <string>
 #include <vector>
 
+#include "q3a/aligner_decoder.h"
 #include "q3a/audio_encoder.h"
 #include "q3a/mel_spectrogram.h"
 
@@ -30,7 +31,7 @@ static bool write_f32(const char* path, const std::vector<float>& v) {
 }
 
 int main(int argc, char** argv) {
-    if (argc < 5) { std::fprintf(stderr, "usage: %s pcm.f32 model.gguf|- mel_out feat_out [asr|aligner]\n", argv[0]); return 1; }
+    if (argc < 5) { std::fprintf(stderr, "usage: %s pcm.f32 model.gguf|- mel_out feat_out [asr|aligner [decoder.gguf logits_out]]\n", argv[0]); return 1; }
     std::vector<float> samples;
     if (!read_f32(argv[1], samples)) { std::fprintf(stderr, "cannot read %s\n", argv[1]); return 1; }
 
@@ -55,5 +56,22 @@ int main(int argc, char** argv) {
     std::vector<float> dummy;
     if (encoder.encode(mel.data.data(), 64, mel.n_len, dummy)) return 4;
     std::printf("mismatch: %s\n", encoder.get_error().c_str());
-    return write_f32(argv[4], audio_features) ? 0 : 1;
+    if (!write_f32(argv[4], audio_features)) return 1;
+    // optional: decoder.gguf logits_out -- ForcedAligner::align's decoder step (forced_aligner.cpp:1661-1690): a prompt of
+    // audio_start + n_audio pads + a few text tokens, the encoder's features spliced in at position 1
+    if (argc > 7) {
+        qwen3_asr::AlignerDecoder decoder;
+        if (!decoder.load_model(argv[6])) { std::fprintf(stderr, "%s\n", decoder.get_error().c_str()); return 5; }
+        const int n_audio = (int)(audio_features.size() / hidden);
+        if (decoder.get_hparams().hidden != hidden) { std::fprintf(stderr, "decoder width differs from the encoder's\n"); return 5; }
+        std::vector<int32_t> tokens((size_t)n_audio + 12);
+        for (size_t i = 0; i < tokens.size(); ++i) tokens[i] = (int32_t)((i * 7 + 3) % (size_t)decoder.get_hparams().vocab);
+        std::vector<float> logits;
+        if (!decoder.forward_decoder(tokens.data(), (int32_t)tokens.size(), audio_features.data(), n_audio, 1, logits)) {
+            std::fprintf(stderr, "%s\n", decoder.get_error().c_str()); return 6;
+        }
+        std::printf("logits %d x %d\n", (int)tokens.size(), decoder.get_hparams().n_classes);
+        if (!write_f32(argv[7], logits)) return 1;
+    }
+    return 0;
 }

@@ -61,3 +61,33 @@ def test_shim_matches_oracle(lib, harness, tmp_path, mode):
     cos = float((got * want).sum() / (np.linalg.norm(got) * np.linalg.norm(want)))
     rel = float(np.abs(got - want).max() / np.abs(want).max())
     assert cos >= 0.999 and rel <= 1e-2, (cos, rel)
+
+
+@pytest.mark.gpu
+def test_shim_decoder_consumes_encoder_features(lib, harness, tmp_path):
+    """mel -> encode_aligner -> forward_decoder through the C++ shims, the order ForcedAligner::align runs them
+    (forced_aligner.cpp:1653-1690), against the two CPU restatements chained the same way."""
+    from q3a_b200 import synth
+    from oracle import decoder_oracle as DO, encoder_oracle as EO, mel_oracle as MO
+    dshape = synth.tiny_decoder_shape()
+    dw = synth.random_decoder_weights(dshape, 3)
+    dgguf = synth.write_decoder_gguf(str(tmp_path / "dec.gguf"), dshape, dw, "f32")
+    shape = synth.tiny_shape(out_dim=dshape.hidden)
+    w = synth.random_weights(shape, 11)
+    gguf = synth.write_gguf(str(tmp_path / "tiny.gguf"), shape, w, "f16")
+    pcm = synth.synth_audio(6, 16000 * 3 + 1234)
+    p = tmp_path / "a.f32"
+    pcm.tofile(p)
+    r = subprocess.run([harness, str(p), gguf, str(tmp_path / "mel.f32"), str(tmp_path / "feat.f32"), "aligner", dgguf,
+                        str(tmp_path / "logits.f32")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    W = EO.Weights(synth.stored_weights(w, "f16"), "f16")
+    feats = EO.encode(MO.log_mel_numpy(pcm, MO.mel_filters_numpy()), W, n_layers=shape.n_layers, d_model=shape.d_model,
+                      n_heads=shape.n_heads, variant="aligner")
+    n = feats.shape[0] + 12
+    tokens = np.array([(i * 7 + 3) % dshape.vocab for i in range(n)], dtype=np.int32)
+    want = DO.forward(tokens, dw, dshape, feats, 1)
+    got = np.fromfile(tmp_path / "logits.f32", dtype=np.float32).reshape(want.shape)
+    cos = float((got * want).sum() / (np.linalg.norm(got) * np.linalg.norm(want)))
+    rel = float(np.abs(got - want).max() / np.abs(want).max())
+    assert cos >= 0.999 and rel <= 1e-2, (cos, rel)
