@@ -37,10 +37,24 @@ fe = B.Frontend(0)
 # config 3: ASR-0.6B, Q8_0 GGUF, 8 x 92-s clips: (a) one 1196-token full-attention sequence per clip, (b) cut into 30-s pieces
 shape = synth.ASR_06B
 w = synth.random_weights(shape, 0)
-enc = B.Encoder(synth.write_gguf(os.path.join(tmp, "asr_q8.gguf"), shape, w, "q8_0"), 0, B.OP_BF16)
-run("config3_q8_92s_full_attention", enc, fe, [92 * 16000] * 8, B.MODE_ASR)
-run("config3_q8_92s_cut_30s", enc, fe, [480000, 480000, 480000, 32000] * 8, B.MODE_ASR)
-enc.close()
+q8_path = synth.write_gguf(os.path.join(tmp, "asr_q8.gguf"), shape, w, "q8_0")
+# row a12: Q8_0 weights resident in HBM and dequantised inside the GEMM, against expanding them at load (Q3A_Q8_DEQUANT_AT_LOAD):
+# weight-arena bytes, single-clip latency, 64-clip throughput
+for tag, env in (("fused", None), ("at_load", "1")):
+    if env:
+        os.environ["Q3A_Q8_DEQUANT_AT_LOAD"] = env
+    else:
+        os.environ.pop("Q3A_Q8_DEQUANT_AT_LOAD", None)
+    enc = B.Encoder(q8_path, 0, B.OP_BF16)
+    res[f"q8_{tag}_weight_bytes"] = enc.device_bytes()
+    print(f"q8 {tag}: weight arena {enc.device_bytes() / 1e6:.1f} MB", flush=True)
+    run(f"q8_{tag}_1x30s_latency", enc, fe, [480000], B.MODE_ASR, reps=8)
+    run(f"q8_{tag}_64x30s", enc, fe, [480000] * 64, B.MODE_ASR)
+    if tag == "fused":
+        run("config3_q8_92s_full_attention", enc, fe, [92 * 16000] * 8, B.MODE_ASR)
+        run("config3_q8_92s_cut_30s", enc, fe, [480000, 480000, 480000, 32000] * 8, B.MODE_ASR)
+    enc.close()
+os.environ.pop("Q3A_Q8_DEQUANT_AT_LOAD", None)
 # config 5 (per-GPU share of the 10-h corpus at 8 GPUs = 4500 s): log-uniform 2-60 s utterances, ASR bf16
 enc = B.Encoder(synth.write_gguf(os.path.join(tmp, "asr_f16.gguf"), shape, w, "f16"), 0, B.OP_BF16)
 rng = np.random.default_rng(500)
