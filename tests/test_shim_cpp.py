@@ -91,3 +91,35 @@ def test_shim_decoder_consumes_encoder_features(lib, harness, tmp_path):
     cos = float((got * want).sum() / (np.linalg.norm(got) * np.linalg.norm(want)))
     rel = float(np.abs(got - want).max() / np.abs(want).max())
     assert cos >= 0.999 and rel <= 1e-2, (cos, rel)
+
+
+@pytest.fixture(scope="module")
+def pool_harness(tmp_path_factory):
+    out = str(tmp_path_factory.mktemp("pool") / "pool_harness")
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Wextra", "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "pool_harness.cpp"), "-o", out, "-L", PKG, "-lq3a", f"-Wl,-rpath,{PKG}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0 and "warning" not in r.stderr, r.stderr
+    return out
+
+
+def test_pool_harness_compiles_and_fails_loudly_without_gpu(lib, pool_harness, tmp_path):
+    if lib.q3a_device_count() == 0:
+        r = subprocess.run([pool_harness, "none.gguf", "2", str(tmp_path / "o.f32")], capture_output=True, text=True)
+        assert r.returncode == 2 and "no CUDA device" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_caller_uses_the_pool_and_the_async_call(lib, pool_harness, tmp_path):
+    """tests/pool_harness.cpp: a single-process C++ caller (the reference's shape, main.cpp:294-504) drives three
+    replicas through q3a_pool_encode_pcm with pinned memory from q3a_host_alloc, then the same clips through two
+    asynchronous calls in flight on one encoder; both must agree bit for bit, and with the Python-side single encoder."""
+    from q3a_b200 import binding as B, synth
+    shape = synth.tiny_shape()
+    gguf = synth.write_gguf(str(tmp_path / "tiny.gguf"), shape, synth.random_weights(shape, 11), "f16")
+    outp = tmp_path / "feat.f32"
+    r = subprocess.run([pool_harness, gguf, "3", str(outp)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr + r.stdout
+    assert "pool == async" in r.stdout
+    got = np.fromfile(outp, dtype=np.float32).reshape(-1, shape.out_dim)
+    assert got.shape[0] > 300 and np.isfinite(got).all()
