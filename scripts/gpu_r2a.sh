@@ -21,6 +21,7 @@ TAIL=8 run q8_pytest timeout 900 $PT -s tests/test_encoder_gpu.py -k "q8"
 TAIL=8 run parity_pytest timeout 1500 $PT -s tests/test_encoder_gpu.py -k "device_entry or pad_rows or full_shape or 30s_clip or batch_invariance or async or merged_copy"
 run pool_pytest timeout 600 $PT tests/test_pool_gpu.py
 TAIL=8 run decoder_pytest timeout 600 $PT tests/test_decoder_gpu.py
+run shim_pytest timeout 600 $PT tests/test_shim_cpp.py
 run bench timeout 900 python bench.py --steps 10 --warmup 3; cat gpurun_out/r2a_bench.log | head -c 6000
 Q3A_NO_LN_FOLD=1 run bench_nofold timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
 Q3A_ATTN_V1=1 run bench_attnv1 timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus
