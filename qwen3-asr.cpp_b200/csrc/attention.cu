@@ -359,8 +359,7 @@ int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnT
 }
 
 int attention_version() {
-    static const int v = getenv("Q3A_ATTN_V1") ? 1 : 2;
-    return v;
+    return feature_enabled("Q3A_ATTN_V2", "Q3A_ATTN_V1", kDefaultAttnV2) ? 2 : 1;    // read per call: tests switch it
 }
 
 }  // namespace q3a

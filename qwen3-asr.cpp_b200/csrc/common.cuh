@@ -187,6 +187,22 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 }
 #endif
 
+// ---- round-2 code paths and their defaults ------------------------------------------------------------------------
+// Each of these replaces a round-1 path that is validated on hardware.  A path becomes the default (constant below set to
+// true) once its parity tests have passed on a B200; until then it is opt-in through the "on" variable.  The "off"
+// variable always wins, so A/B runs work in both states.  tests/validated_on_b200.json mirrors the constants.
+constexpr bool kDefaultAttnV2 = false;       // attention2.cu instead of attention.cu          Q3A_ATTN_V2 / Q3A_ATTN_V1
+                                             // (validated r2a: all 76 parity cases green, but 157 us against 133 us per
+                                             //  layer on the bench shape -- DESIGN.md 4.4 -- so the first kernel stays default)
+constexpr bool kDefaultLnFold = true;        // LayerNorm folded into the GEMMs                Q3A_LN_FOLD / Q3A_NO_LN_FOLD
+constexpr bool kDefaultQ8Fused = true;       // Q8_0 weights dequantised inside the GEMM       Q3A_Q8_FUSED / Q3A_Q8_DEQUANT_AT_LOAD
+constexpr bool kDefaultConvCbMajor = true;   // channel-block-major K order in conv2 / conv3   Q3A_CONV_CB_MAJOR / Q3A_CONV_TAP_MAJOR
+inline bool feature_enabled(const char* env_on, const char* env_off, bool dflt) {
+    if (getenv(env_off)) return false;
+    if (getenv(env_on)) return true;
+    return dflt;
+}
+
 // make `device` current and check that it is an sm_100 part (there is no other code path)
 int use_device(int device);
 // opt a kernel in to `bytes` of dynamic shared memory, once per (kernel, current device); thread-safe (several encoders

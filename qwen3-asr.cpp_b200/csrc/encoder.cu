@@ -488,7 +488,7 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
     hp.weight_ftype = (int)t_up->type;
     // Q8_0 files keep their Linear weights quantised on the device unless Q3A_Q8_DEQUANT_AT_LOAD is set; gamma cannot be
     // folded into 32-element blocks that share one scale, so that path runs the separate LayerNorm kernel
-    e->q8_fused = hp.weight_ftype == (int)GGML_Q8_0 && getenv("Q3A_Q8_DEQUANT_AT_LOAD") == nullptr;
+    e->q8_fused = hp.weight_ftype == (int)GGML_Q8_0 && feature_enabled("Q3A_Q8_FUSED", "Q3A_Q8_DEQUANT_AT_LOAD", kDefaultQ8Fused);
     if (e->q8_fused) e->ln_fold = false;
     const int d = hp.d_model, C = hp.conv_channels, ffn = hp.ffn_dim, F3 = hp.n_mel_bins / 8;
     if (hp.n_mel_bins != 128) { set_error("only 128 mel bins are supported"); return Q3A_ERR_FORMAT; }
@@ -667,7 +667,7 @@ extern "C" int q3a_encoder_load(const char* gguf_path, int device, int operand_d
     Q3A_TRY(use_device(device));
     q3a_encoder* e = new q3a_encoder();
     e->device = device; e->fmt = operand_dtype;
-    e->ln_fold = getenv("Q3A_NO_LN_FOLD") == nullptr;       // A/B switch: separate layernorm_kernel launches instead
+    e->ln_fold = feature_enabled("Q3A_LN_FOLD", "Q3A_NO_LN_FOLD", kDefaultLnFold);   // else separate layernorm_kernel launches
     int rc = load_weights(e, f);
     if (rc == Q3A_OK) {
         bool ok = cudaStreamCreateWithFlags(&e->stream, cudaStreamNonBlocking) == cudaSuccess &&

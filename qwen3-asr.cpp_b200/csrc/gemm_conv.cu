@@ -30,8 +30,7 @@ static int launch_conv(const ConvArgs& a, const Epi& epi, cudaStream_t stream) {
     loader.c_blocks = c_blocks;
     loader.rows_per_tile = kBlockM / a.Fh;
     loader.last_block_steps = ceil_div(a.C - (c_blocks - 1) * kBlockK, kUmmaK);
-    static const int tap_major = getenv("Q3A_CONV_TAP_MAJOR") != nullptr;       // A/B switch: the round-1 K order
-    loader.cb_major = tap_major ? 0 : 1;
+    loader.cb_major = feature_enabled("Q3A_CONV_CB_MAJOR", "Q3A_CONV_TAP_MAJOR", kDefaultConvCbMajor) ? 1 : 0;
     const int M = a.R_used * a.Fh;
     const int tiles = ceil_div(M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
     const int grid = 2 * (tiles < pairs ? tiles : pairs);

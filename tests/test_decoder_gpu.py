@@ -13,7 +13,9 @@ from oracle import decoder_oracle as DO, encoder_oracle as EO, mel_oracle as MO
 from q3a_b200 import binding as B, synth
 from conftest import compare
 
-pytestmark = pytest.mark.gpu
+from conftest import needs  # noqa: E402
+
+pytestmark = [pytest.mark.gpu, needs("decoder")]
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 sys.path.insert(0, GOLD)
 COS, REL = 0.999, 1e-2

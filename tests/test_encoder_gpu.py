@@ -8,7 +8,7 @@ import pytest
 
 from oracle import encoder_oracle as EO, mel_oracle as MO
 from q3a_b200 import binding as B, synth
-from conftest import compare
+from conftest import compare, needs
 
 pytestmark = pytest.mark.gpu
 COS, REL = 0.999, 1e-2
@@ -213,7 +213,7 @@ def test_pcm_path_batch_invariance_and_full_size(lib, asr_model, filters):
     cos, rel = compare(outs[5], want)
     assert cos >= COS and rel <= REL, (cos, rel)
     tm = enc.timings()
-    assert tm.total_launches > 100
+    assert tm.total_launches > 90          # 98 with LayerNorm folded into the GEMMs (135 with the separate kernel)
     enc.close(); fe.close()
 
 
@@ -469,6 +469,7 @@ def test_q8_file_three_way_at_real_width(lib, asr_model, filters):
         assert cos_ac >= COS and rel_ac <= rel_ab + rel_cb + 1e-3, (cos_ac, rel_ac)
 
 
+@needs("q8_fused")
 def test_q8_fused_dequant_is_bit_identical_to_dequant_at_load(lib, tiny_models, asr_model, filters, monkeypatch):
     """Row a12: with a Q8_0 file the Linear weights stay quantised in device memory (int8 plane + f16 block scales, 34 bytes
     per 32 weights as in the GGUF) and the GEMM's dequant warps expand them into the operand stage.  The value they
@@ -480,7 +481,9 @@ def test_q8_fused_dequant_is_bit_identical_to_dequant_at_load(lib, tiny_models, 
     mel_big = MO.log_mel_numpy(synth.synth_audio(303, 16000 * 7 + 123), filters)
     for path, mels, opd in ((models["q8_0"][0], mels_tiny, B.OP_F16), (models["q8_0"][0], mels_tiny, B.OP_BF16),
                             (paths["q8_0"], [mel_big], B.OP_BF16)):
+        monkeypatch.setenv("Q3A_Q8_FUSED", "1")
         fused = B.Encoder(path, 0, opd)
+        monkeypatch.delenv("Q3A_Q8_FUSED")
         bytes_fused = fused.device_bytes()
         got = fused.encode_batch(mels, B.MODE_ASR)
         fused.close()
@@ -498,6 +501,7 @@ def test_q8_fused_dequant_is_bit_identical_to_dequant_at_load(lib, tiny_models, 
             assert bytes_fused < 0.62 * bytes_plain
 
 
+@needs("async_call")
 def test_async_submit_wait_matches_synchronous_call(lib, asr_model):
     """q3a_encode_pcm_submit / q3a_encode_wait: four calls over different ragged batches with two in flight at any time
     (call k+1 is submitted before call k is waited for, so its upload and stem overlap call k's tail); every call's
@@ -557,3 +561,50 @@ def test_contiguous_host_blocks_take_the_merged_copy_path(lib, tiny_models):
     for a, b in zip(outs, want):
         assert np.array_equal(a, b)
     enc.close(); fe.close()
+
+
+@needs("ln_fold")
+@pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
+def test_layernorm_fold_matches_the_separate_kernel(lib, tiny_models, asr_model, filters, monkeypatch, opd):
+    """LayerNorm folded into the QKV / FFN-up / proj1 GEMMs (epilogues.cuh) against the separate layernorm_kernel path:
+    both must meet the tolerance against the oracle, agree with each other far inside it, and the folded path must stay
+    batch-invariant (its row statistics are partial sums added in a fixed order)."""
+    _, models = tiny_models
+    shape, paths, Ws = asr_model
+    mel = MO.log_mel_numpy(synth.synth_audio(305, 16000 * 9 + 4321), filters)
+    others = [MO.log_mel_numpy(synth.synth_audio(306 + i, 16000 * (2 + 3 * i)), filters) for i in range(3)]
+    want = _oracle(mel, Ws["f16"], shape, "asr")
+    outs = {}
+    for name, env in (("fold", "Q3A_LN_FOLD"), ("separate", "Q3A_NO_LN_FOLD")):
+        monkeypatch.setenv(env, "1")
+        enc = B.Encoder(paths["f16"], 0, opd)
+        monkeypatch.delenv(env)
+        outs[name] = enc.encode_batch([mel], B.MODE_ASR)[0]
+        if name == "fold":
+            assert np.array_equal(enc.encode_batch(others + [mel], B.MODE_ASR)[-1], outs[name])      # batch-invariant
+            assert enc.timings().total_launches < 18 * 6 + 12                                          # no LayerNorm launches
+        enc.close()
+        cos, rel = compare(outs[name], want)
+        assert cos >= COS and rel <= REL, (name, cos, rel)
+    cos, rel = compare(outs["fold"], outs["separate"])
+    assert cos >= 0.99999 and rel <= (6e-3 if opd == B.OP_BF16 else 1e-3), (cos, rel)
+
+
+@needs("conv_cb_major")
+def test_conv_k_order_only_changes_the_summation_order(lib, asr_model, filters, monkeypatch):
+    """conv2 / conv3 walk K channel-block-major (L2 reuse of the nine taps) or tap-major (round 1): same products, another
+    fp32 summation order, so the features agree to rounding noise and both meet the tolerance."""
+    shape, paths, Ws = asr_model
+    mel = MO.log_mel_numpy(synth.synth_audio(307, 16000 * 6 + 77), filters)
+    want = _oracle(mel, Ws["f16"], shape, "asr")
+    outs = []
+    for env in ("Q3A_CONV_CB_MAJOR", "Q3A_CONV_TAP_MAJOR"):
+        monkeypatch.setenv(env, "1")
+        enc = B.Encoder(paths["f16"], 0, B.OP_F16)
+        outs.append(enc.encode_batch([mel], B.MODE_ASR)[0])
+        enc.close()
+        monkeypatch.delenv(env)
+        cos, rel = compare(outs[-1], want)
+        assert cos >= COS and rel <= REL, (env, cos, rel)
+    cos, rel = compare(outs[0], outs[1])
+    assert cos >= 0.999999 and rel <= 1e-3, (cos, rel)

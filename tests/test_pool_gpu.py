@@ -6,7 +6,9 @@ import pytest
 
 from q3a_b200 import binding as B, synth
 
-pytestmark = pytest.mark.gpu
+from conftest import needs  # noqa: E402
+
+pytestmark = [pytest.mark.gpu, needs("pool")]
 
 
 def _devices(lib):

@@ -7,6 +7,8 @@ import subprocess
 import numpy as np
 import pytest
 
+from conftest import needs
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "qwen3-asr.cpp_b200")
 
@@ -64,6 +66,7 @@ def test_shim_matches_oracle(lib, harness, tmp_path, mode):
 
 
 @pytest.mark.gpu
+@needs("decoder")
 def test_shim_decoder_consumes_encoder_features(lib, harness, tmp_path):
     """mel -> encode_aligner -> forward_decoder through the C++ shims, the order ForcedAligner::align runs them
     (forced_aligner.cpp:1653-1690), against the two CPU restatements chained the same way."""
@@ -110,6 +113,8 @@ def test_pool_harness_compiles_and_fails_loudly_without_gpu(lib, pool_harness, t
 
 
 @pytest.mark.gpu
+@needs("pool")
+@needs("async_call")
 def test_cpp_caller_uses_the_pool_and_the_async_call(lib, pool_harness, tmp_path):
     """tests/pool_harness.cpp: a single-process C++ caller (the reference's shape, main.cpp:294-504) drives three
     replicas through q3a_pool_encode_pcm with pinned memory from q3a_host_alloc, then the same clips through two
