@@ -13,7 +13,11 @@ CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-corpus"
 timeout 300 $CMD > gpurun_out/plain.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --print-units base --clock-control none -k regex:'q3a|mel|conv1|attention|gemm|layernorm|pcm16' -c 2000 --csv --log-file gpurun_out/launches_all.csv $CMD > gpurun_out/ncu_launches.log 2>&1
 echo "ncu launches exit=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:attention2 -s 40 -c 2 -f -o gpurun_out/prof_attn2 $CMD > gpurun_out/ncu_attn.log 2>&1; echo "ncu attn exit=$?"
+Q3A_NO_LN_FOLD=1 timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --print-units base --clock-control none -k regex:'q3a|mel|conv1|attention|gemm|layernorm|pcm16' -c 700 --csv --log-file gpurun_out/launches_nofold.csv $CMD > gpurun_out/ncu_launches_nofold.log 2>&1
+echo "ncu launches (no fold) exit=$?"
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:attention_kernel -s 40 -c 2 -f -o gpurun_out/prof_attn1 $CMD > gpurun_out/ncu_attn.log 2>&1; echo "ncu attn v1 exit=$?"
+ACMD="python scripts/gpu_attn_bench.py"
+ATTN_V=2 ATTN_POLY=0 ATTN_L=390 timeout 600 ncu --set full --clock-control none --import-source on -k regex:attention2 -s 4 -c 2 -f -o gpurun_out/prof_attn2 $ACMD > gpurun_out/ncu_attn2.log 2>&1; echo "ncu attn v2 exit=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:gemm_tc -s 300 -c 8 -f -o gpurun_out/prof_gemm $CMD > gpurun_out/ncu_gemm.log 2>&1; echo "ncu gemm exit=$?"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:mel_frames -s 3 -c 1 -f -o gpurun_out/prof_mel $CMD > gpurun_out/ncu_mel.log 2>&1; echo "ncu mel exit=$?"
 ls -la gpurun_out | tail -20
