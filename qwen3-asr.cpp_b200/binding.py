@@ -82,6 +82,7 @@ SYMBOLS = {
     "q3a_test_gemm": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "q3a_test_attention": (_I, [_P, _P, _I, _I, _P, _I, _I, _P]),
     "q3a_test_attention_v": (_I, [_P, _P, _I, _I, _P, _I, _I, _I, _P]),
+    "q3a_probe_mma_rate": (_I, [_I, _I, _I, _I, _I, _I, _P, _P]),
     "q3a_debug_check_guards": (_I, [_P, _P]),
     "q3a_debug_damage_guard": (_I, []),
 }
