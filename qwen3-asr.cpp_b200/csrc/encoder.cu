@@ -864,7 +864,11 @@ static int run_host_passes(q3a_encoder* e, const void* const* in, const int* in_
                            std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_begin).count());
     };
     HostPlan plan;
-    plan_host_call(in_elems, elem_bytes, align_elems, n_frames, n, mode, width, getenv("Q3A_NO_PART_OVERLAP") == nullptr, plan);
+    // Intra-call parts overlap a call's own copies with its own kernels: what a synchronous caller needs.  With calls in
+    // flight back to back (submit / wait) the next call's upload and the previous call's download already run under this
+    // call's kernels, and the parts would only cut the launches into smaller, less efficient ones; Q3A_ASYNC_PARTS=1 keeps them.
+    const bool parts = getenv("Q3A_NO_PART_OVERLAP") == nullptr && (wait || getenv("Q3A_ASYNC_PARTS") != nullptr);
+    plan_host_call(in_elems, elem_bytes, align_elems, n_frames, n, mode, width, parts, plan);
     const std::vector<int>& bounds = plan.bounds;
     const std::vector<std::vector<int64_t>>& ioff = plan.ioff;
     const std::vector<std::vector<int>>&in_split = plan.in_split, &out_split = plan.out_split;
