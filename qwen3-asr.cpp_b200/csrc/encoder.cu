@@ -279,6 +279,7 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
     // LayerNorm fold (epilogues.cuh): `out16` / `stats` are the 16-bit copy and the statistics partials of the residual
     // stream for the rows of this launch (producers write them, LNFOLD consumers read `stats` and `colsum`)
     const bool fold = e->ln_fold;
+    const bool fold1 = e->fold_mask & 1, fold2 = e->fold_mask & 2, foldp = e->fold_mask & 4;
     const int n_part = fold ? ln_partials(d) : 0;
     auto linear = [&](EpiKind kind, const void* A, int K, const q3a_encoder::Wt& W, int N, void* out, const float* bias,
                       const float* res, const float* pe_tab, const int* pos_tab, int rows, void* out16 = nullptr,
@@ -352,7 +353,7 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         if (mode == Q3A_MODE_CONV_ONLY)
             Q3A_TRY(linear(EPI_POSEMB_F32, rows16(e->feat.p, feat_dim, t0), feat_dim, q3a_encoder::Wt{e->conv_out_w, nullptr}, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, nullptr, nullptr, tn));
-        else if (fold)
+        else if (fold1)
             Q3A_TRY(linear(EPI_POSEMB_F32_DUAL, rows16(e->feat.p, feat_dim, t0), feat_dim, q3a_encoder::Wt{e->conv_out_w, nullptr}, d, stem_out + (size_t)t0 * d,
                            nullptr, nullptr, e->pe.as<float>(), d_pos + t0, tn, rows16(e->h.p, d, t0),
                            e->stats.as<float2>() + (size_t)t0 * n_part));
@@ -400,25 +401,30 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         void* qkvr = rows16(e->qkv.p, 3 * (size_t)d, t0);
         for (int li = l0; li < l1; ++li) {
             const auto& L = e->layers[li];
-            if (fold) {
-                // h holds the residual stream rounded to 16 bits, `stats` its row sums: no LayerNorm kernel
+            // Folded sites take the residual stream's 16-bit copy (h) and its row statistics from the GEMM that produced it;
+            // the others run the LayerNorm kernel into h.  A producer emits copy + statistics when the next consumer folds.
+            const bool last = li + 1 == (int)e->layers.size();
+            const bool next1 = last ? foldp : fold1;               // what consumes the stream after this layer
+            if (fold1) {
                 Q3A_TRY(linear(EPI_LNFOLD_OP, hr, d, L.w_qkv, 3 * d, qkvr, L.b_qkv, nullptr, nullptr, nullptr, tn, nullptr, str, L.s_qkv));
-                Q3A_TRY(attention());
+            } else {
+                Q3A_TRY(ln(L.ln1_g, L.ln1_b));
+                Q3A_TRY(linear(EPI_BIAS_OP, hr, d, L.w_qkv, 3 * d, qkvr, L.b_qkv, nullptr, nullptr, nullptr, tn));
+            }
+            Q3A_TRY(attention());
+            if (fold2) {
                 Q3A_TRY(linear(EPI_BIAS_RES_F32_DUAL, attr, d, L.w_o, d, xr, L.b_o, xr, nullptr, nullptr, tn, hr, str));
                 Q3A_TRY(linear(EPI_LNFOLD_GELU_OP, hr, d, L.w_up, ffn, upr, L.b_up, nullptr, nullptr, nullptr, tn, nullptr, str, L.s_up));
-                Q3A_TRY(linear(EPI_BIAS_RES_F32_DUAL, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn, hr, str));
-                continue;
+            } else {
+                Q3A_TRY(linear(EPI_BIAS_RES_F32, attr, d, L.w_o, d, xr, L.b_o, xr, nullptr, nullptr, tn));
+                Q3A_TRY(ln(L.ln2_g, L.ln2_b));
+                Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, L.w_up, ffn, upr, L.b_up, nullptr, nullptr, nullptr, tn));
             }
-            Q3A_TRY(ln(L.ln1_g, L.ln1_b));
-            Q3A_TRY(linear(EPI_BIAS_OP, hr, d, L.w_qkv, 3 * d, qkvr, L.b_qkv, nullptr, nullptr, nullptr, tn));
-            Q3A_TRY(attention());
-            Q3A_TRY(linear(EPI_BIAS_RES_F32, attr, d, L.w_o, d, xr, L.b_o, xr, nullptr, nullptr, tn));
-            Q3A_TRY(ln(L.ln2_g, L.ln2_b));
-            Q3A_TRY(linear(EPI_BIAS_GELU_OP, hr, d, L.w_up, ffn, upr, L.b_up, nullptr, nullptr, nullptr, tn));
-            Q3A_TRY(linear(EPI_BIAS_RES_F32, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn));
+            if (next1) Q3A_TRY(linear(EPI_BIAS_RES_F32_DUAL, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn, hr, str));
+            else Q3A_TRY(linear(EPI_BIAS_RES_F32, upr, ffn, L.w_down, d, xr, L.b_down, xr, nullptr, nullptr, tn));
         }
         if (post) {
-            if (fold) {
+            if (foldp) {
                 Q3A_TRY(linear(EPI_LNFOLD_GELU_OP, hr, d, e->w_p1, d, attr, e->b_p1, nullptr, nullptr, nullptr, tn, nullptr, str, e->s_p1));
             } else {
                 Q3A_TRY(ln(e->lnp_g, e->lnp_b));
@@ -490,6 +496,9 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
     // folded into 32-element blocks that share one scale, so that path runs the separate LayerNorm kernel
     e->q8_fused = hp.weight_ftype == (int)GGML_Q8_0 && feature_enabled("Q3A_Q8_FUSED", "Q3A_Q8_DEQUANT_AT_LOAD", kDefaultQ8Fused);
     if (e->q8_fused) e->ln_fold = false;
+    // Q3A_LN_FOLD_MASK=<1..7> folds only some of the three LayerNorm sites (experiments; the others keep the kernel)
+    e->fold_mask = e->ln_fold ? 7 : 0;
+    if (e->ln_fold) if (const char* m = getenv("Q3A_LN_FOLD_MASK")) { e->fold_mask = atoi(m) & 7; e->ln_fold = e->fold_mask != 0; }
     const int d = hp.d_model, C = hp.conv_channels, ffn = hp.ffn_dim, F3 = hp.n_mel_bins / 8;
     if (hp.n_mel_bins != 128) { set_error("only 128 mel bins are supported"); return Q3A_ERR_FORMAT; }
     if (hp.n_attention_heads * 64 != d) { set_error("head_dim must be 64 (d_model = 64 * heads)"); return Q3A_ERR_FORMAT; }
@@ -571,7 +580,7 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
         return true;
     };
 #define LINEAR(...) do { if (!add_linear(__VA_ARGS__)) { set_error(err); return Q3A_ERR_FORMAT; } } while (0)
-    const bool fold = e->ln_fold;
+    const bool fold1 = e->fold_mask & 1, fold2 = e->fold_mask & 2, foldp = e->fold_mask & 4;
     e->layers.assign(hp.n_encoder_layers, q3a_encoder::Layer{});
     for (int l = 0; l < hp.n_encoder_layers; ++l) {
         auto& L = e->layers[l];
@@ -581,14 +590,14 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
         FETCH(B + "attn_norm.bias", b1, d);   plan.add_f32(&L.ln1_b, b1);
         FETCH(B + "attn_q.bias", v, d); FETCH(B + "attn_k.bias", v2, d); FETCH(B + "attn_v.bias", v3, d);
         bias = v; bias.insert(bias.end(), v2.begin(), v2.end()); bias.insert(bias.end(), v3.begin(), v3.end());
-        LINEAR(&L.w_qkv, {B + "attn_q.weight", B + "attn_k.weight", B + "attn_v.weight"}, d, d, fold ? &g1 : nullptr, &b1, &bias, &L.s_qkv);
+        LINEAR(&L.w_qkv, {B + "attn_q.weight", B + "attn_k.weight", B + "attn_v.weight"}, d, d, fold1 ? &g1 : nullptr, &b1, &bias, &L.s_qkv);
         plan.add_f32(&L.b_qkv, bias);
         LINEAR(&L.w_o, {B + "attn_out.weight"}, d, d, nullptr, nullptr, nullptr, nullptr);
         FETCH(B + "attn_out.bias", v, d);                plan.add_f32(&L.b_o, v);
         FETCH(B + "ffn_norm.weight", g2, d); plan.add_f32(&L.ln2_g, g2);
         FETCH(B + "ffn_norm.bias", b2, d);   plan.add_f32(&L.ln2_b, b2);
         FETCH(B + "ffn_up.bias", bias, ffn);
-        LINEAR(&L.w_up, {B + "ffn_up.weight"}, ffn, d, fold ? &g2 : nullptr, &b2, &bias, &L.s_up);
+        LINEAR(&L.w_up, {B + "ffn_up.weight"}, ffn, d, fold2 ? &g2 : nullptr, &b2, &bias, &L.s_up);
         plan.add_f32(&L.b_up, bias);
         LINEAR(&L.w_down, {B + "ffn_down.weight"}, d, ffn, nullptr, nullptr, nullptr, nullptr);
         FETCH(B + "ffn_down.bias", v, d);                  plan.add_f32(&L.b_down, v);
@@ -598,7 +607,7 @@ static int load_weights(q3a_encoder* e, const GgufFile& f) {
         FETCH("ln_post.weight", gp, d); plan.add_f32(&e->lnp_g, gp);
         FETCH("ln_post.bias", bp, d);   plan.add_f32(&e->lnp_b, bp);
         FETCH("proj1.bias", bias, d);
-        LINEAR(&e->w_p1, {"proj1.weight"}, d, d, fold ? &gp : nullptr, &bp, &bias, &e->s_p1);
+        LINEAR(&e->w_p1, {"proj1.weight"}, d, d, foldp ? &gp : nullptr, &bp, &bias, &e->s_p1);
         plan.add_f32(&e->b_p1, bias);
     }
     LINEAR(&e->w_p2, {"proj2.weight"}, hp.out_dim, d, nullptr, nullptr, nullptr, nullptr);

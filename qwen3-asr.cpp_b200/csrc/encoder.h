@@ -44,6 +44,7 @@ struct q3a_encoder {
     bool q8_fused = false;           // Linear weights stay Q8_0 in device memory, dequantised inside the GEMM (gemm_tc.cuh kWq8)
     const float* s_p1 = nullptr;
     bool ln_fold = false;            // LayerNorm folded into the QKV / FFN-up / proj1 GEMMs (no layernorm_kernel launches)
+    int fold_mask = 0;               // which of them: 1 = attn_norm -> QKV, 2 = ffn_norm -> FFN-up, 4 = ln_post -> proj1 (7 = all)
     q3a::DevBuf pe;                  // sinusoidal table [pe_rows][d_model] f32
     int pe_rows = 0;
 
