@@ -7,6 +7,9 @@ timeout 2400 python -m pytest tests -x -q -m gpu > gpurun_out/r2b_pytest.log 2>&
 timeout 300 python __graft_entry__.py --smoke > gpurun_out/r2b_smoke.log 2>&1; echo "smoke exit=$?"; tail -3 gpurun_out/r2b_smoke.log
 timeout 900 python bench.py > gpurun_out/r2b_bench.json 2> gpurun_out/r2b_bench.err; echo "bench exit=$?"; cat gpurun_out/r2b_bench.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2b_bench_ref.json 2> gpurun_out/r2b_bench_ref.err; echo "bench ref exit=$?"; cat gpurun_out/r2b_bench_ref.json
+for V in "Q3A_LN_FOLD_MASK=1" "Q3A_LN_FOLD_MASK=2" "Q3A_NO_LN_FOLD=1" "Q3A_ATTN_V2=1" "Q3A_CONV_TAP_MAJOR=1"; do
+  env $V timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus > "gpurun_out/r2b_bench_ab_${V%%=*}_${V##*=}.json" 2>/dev/null; echo "bench $V exit=$?"
+done
 timeout 300 python scripts/gpu_mma_probe.py > gpurun_out/r2b_mma_probe.log 2>&1; echo "mma probe exit=$?"; tail -40 gpurun_out/r2b_mma_probe.log
 timeout 300 python scripts/gpu_attn_bench.py > gpurun_out/r2b_attn_bench.log 2>&1; echo "attn bench exit=$?"
 timeout 1200 python scripts/gpu_configs.py > gpurun_out/r2b_configs.log 2>&1; echo "configs exit=$?"; tail -12 gpurun_out/r2b_configs.log
