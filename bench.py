@@ -320,10 +320,18 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device — the product has no CPU path (use --impl reference for the CPU arm)")
     from q3a_b200 import hostbind
     # before any pinned allocation: buffers land on the GPU's NUMA node (Q3A_BENCH_NO_BIND=1 for an A/B run)
+    # Functional check of the multi-rank path on a box with fewer GPUs than ranks (development only, flagged in the line):
+    # ranks share GPUs and the bookkeeping collectives go over gloo; there is no collective on the compute path either way.
+    n_dev = torch.cuda.device_count()
+    emulated = world > n_dev
+    local = local % n_dev
     binding_info = {"bound": False, "why_not": "Q3A_BENCH_NO_BIND"} if os.environ.get("Q3A_BENCH_NO_BIND") else hostbind.bind_to_gpu(local)
     torch.cuda.set_device(local)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        if emulated:
+            dist.init_process_group("gloo")
+        else:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B.load()
 
     tmpdir = os.path.join(tempfile.gettempdir(), "q3a_bench")
@@ -537,6 +545,7 @@ def run_ours(args):
                 "synchronous_call_value": e2e_sync_value,
                 "synchronous_api": "q3a_encode_pcm_batch, one call at a time"},
         "gpu_launches": launches0,
+        "ranks_share_gpus": emulated,
         "value_checked": value_checked, "value_check": {"against": "q3a_encode_pcm_batch on the same 64 clips (host result)",
                                                          "max_abs_diff": max_diff, "rows": int(got.shape[0])},
         "clocks": clocks,

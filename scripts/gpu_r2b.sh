@@ -10,6 +10,7 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r
 for V in "Q3A_LN_FOLD_MASK=1" "Q3A_LN_FOLD_MASK=2" "Q3A_NO_LN_FOLD=1" "Q3A_ATTN_V2=1" "Q3A_CONV_TAP_MAJOR=1"; do
   env $V timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus > "gpurun_out/r2b_bench_ab_${V%%=*}_${V##*=}.json" 2>/dev/null; echo "bench $V exit=$?"
 done
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 2 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2b_bench_2ranks_1gpu.json 2> gpurun_out/r2b_bench_2ranks_1gpu.err; echo "2-rank functional bench exit=$?"; tail -c 1500 gpurun_out/r2b_bench_2ranks_1gpu.json
 timeout 300 python scripts/gpu_mma_probe.py > gpurun_out/r2b_mma_probe.log 2>&1; echo "mma probe exit=$?"; tail -40 gpurun_out/r2b_mma_probe.log
 timeout 300 python scripts/gpu_attn_bench.py > gpurun_out/r2b_attn_bench.log 2>&1; echo "attn bench exit=$?"
 timeout 1200 python scripts/gpu_configs.py > gpurun_out/r2b_configs.log 2>&1; echo "configs exit=$?"; tail -12 gpurun_out/r2b_configs.log
