@@ -55,6 +55,7 @@ struct EpiBiasF32 {
     static constexpr bool kStaged = true, kResidual = kRes;
     static constexpr int kOutBytes = 4;
     const float* bias;
+    int prefetch = 1;        // residual epilogues: L2-prefetch the next tile's residual rows (gemm_tc.cuh)
     __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
         if (!bias) return;
 #pragma unroll
@@ -105,6 +106,7 @@ struct EpiBiasF32Dual {
     static constexpr int kOutBytes = 4;
     const float* bias;
     float2* stats; int n_part;
+    int prefetch = 1;
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
     __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
         if (!bias) return;

@@ -40,6 +40,9 @@ int gemm_prepare_impl(const void* kernel, int smem_bytes, int threads, int* max_
     return Q3A_OK;
 }
 
+// Q3A_NO_RES_PREFETCH: A/B switch for the residual epilogues' L2 prefetch of the next tile
+static int res_prefetch() { return getenv("Q3A_NO_RES_PREFETCH") ? 0 : 1; }
+
 int ln_partials(int N) {
     int bn = pick_block_n(N);
     if (bn == 240) bn = 128;
@@ -106,7 +109,7 @@ static int dispatch_epi_q8(EpiKind kind, const LinearArgs& a, cudaStream_t strea
         case EPI_BIAS_F32: return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasF32<false>{a.bias}, stream);
         case EPI_BIAS_RES_F32:
             if (a.res != a.out) { set_error("gemm_linear: the residual must be the output matrix (updated in place)"); return Q3A_ERR_ARG; }
-            return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias}, stream);
+            return launch_linear_q8<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias, res_prefetch()}, stream);
         default: break;
     }
     set_error("gemm_linear: this epilogue has no fused-Q8_0 instantiation");
@@ -126,7 +129,7 @@ static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) 
             return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<false>{a.bias}, stream);
         case EPI_BIAS_RES_F32:
             if (a.res != a.out) { set_error("gemm_linear: the residual must be the output matrix (updated in place)"); return Q3A_ERR_ARG; }
-            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32<true>{a.bias, res_prefetch()}, stream);
         case EPI_POSEMB_F32:
             return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32{a.pe, a.pos, a.ldc, a.M}, stream);
         case EPI_BIAS_RES_F32_DUAL:
@@ -137,7 +140,7 @@ static int dispatch_epi(EpiKind kind, const LinearArgs& a, cudaStream_t stream) 
             if (kind == EPI_POSEMB_F32_DUAL)
                 return launch_linear<BLOCK_N, kFmt>(a, EpiPosEmbF32Dual<OpT>{a.pe, a.pos, a.ldc, a.M, a.stats, a.n_part}, stream);
             if (a.res != a.out) { set_error("gemm_linear: the residual must be the output matrix (updated in place)"); return Q3A_ERR_ARG; }
-            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32Dual<OpT, true>{a.bias, a.stats, a.n_part}, stream);
+            return launch_linear<BLOCK_N, kFmt>(a, EpiBiasF32Dual<OpT, true>{a.bias, a.stats, a.n_part, res_prefetch()}, stream);
         case EPI_LNFOLD_OP:
         case EPI_LNFOLD_GELU_OP:
             if (!a.bias || !a.colsum || !a.stats || a.n_part <= 0) { set_error("gemm_linear: LayerNorm fold needs bias', colsum and stats"); return Q3A_ERR_ARG; }

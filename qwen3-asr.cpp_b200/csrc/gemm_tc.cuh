@@ -387,6 +387,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const int as = local & 1;
             const uint32_t aph = (local >> 1) & 1;
             const int nch = chunks_of(n_blk);
+            if constexpr (kResidual) {
+                // The residual stream was written two or three kernels ago and has left L2 since: start this warp's chunks of
+                // the pair's NEXT tile on their way from HBM now, a whole tile ahead of the shared-memory loads that use them.
+                const int nt = tile + num_pairs;
+                if (lane == 0 && nt < num_tiles && epi.prefetch) {
+                    const int m_n = nt / n_blocks, n_n = nt - m_n * n_blocks;
+                    const int nch_n = chunks_of(n_n);
+                    for (int c = hf; c < nch_n; c += 2)
+                        tc::tma_prefetch_2d(&tmap_c, n_n * BLOCK_N + c * 32, (2 * m_n + (int)rank) * kBlockM + q * 32);
+                }
+            }
             tc::mbar_wait(tfull_bar(as), aph);
             tc::fence_after_sync();
             const int m0 = (2 * m_blk + (int)rank) * kBlockM + q * 32;
