@@ -7,7 +7,7 @@ timeout 2400 python -m pytest tests -x -q -m gpu > gpurun_out/r2b_pytest.log 2>&
 timeout 300 python __graft_entry__.py --smoke > gpurun_out/r2b_smoke.log 2>&1; echo "smoke exit=$?"; tail -3 gpurun_out/r2b_smoke.log
 timeout 900 python bench.py > gpurun_out/r2b_bench.json 2> gpurun_out/r2b_bench.err; echo "bench exit=$?"; cat gpurun_out/r2b_bench.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2b_bench_ref.json 2> gpurun_out/r2b_bench_ref.err; echo "bench ref exit=$?"; cat gpurun_out/r2b_bench_ref.json
-for V in "Q3A_LN_FOLD_MASK=1" "Q3A_LN_FOLD_MASK=2" "Q3A_NO_LN_FOLD=1" "Q3A_ATTN_V2=1" "Q3A_CONV_TAP_MAJOR=1"; do
+for V in "Q3A_LN_FOLD_MASK=1" "Q3A_LN_FOLD_MASK=2" "Q3A_NO_LN_FOLD=1" "Q3A_ATTN_V2=1" "Q3A_CONV_TAP_MAJOR=1" "Q3A_NO_RES_PREFETCH=1"; do
   env $V timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-corpus > "gpurun_out/r2b_bench_ab_${V%%=*}_${V##*=}.json" 2>/dev/null; echo "bench $V exit=$?"
 done
 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29517 bench.py --gpus 2 --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/r2b_bench_2ranks_1gpu.json 2> gpurun_out/r2b_bench_2ranks_1gpu.err; echo "2-rank functional bench exit=$?"; tail -c 1500 gpurun_out/r2b_bench_2ranks_1gpu.json
