@@ -3,7 +3,7 @@
 # bench step; --set full captures of the attention and GEMM kernels).  ncu only after the same command exited 0 plain.
 set -u
 mkdir -p gpurun_out
-timeout 2400 python -m pytest tests -x -q -m gpu > gpurun_out/r2b_pytest.log 2>&1; echo "pytest exit=$?" | tee -a gpurun_out/r2b_pytest.log; tail -4 gpurun_out/r2b_pytest.log
+timeout 2400 python -m pytest tests -q -m gpu -rf > gpurun_out/r2b_pytest.log 2>&1; echo "pytest exit=$?" | tee -a gpurun_out/r2b_pytest.log; grep -E "^(E  |FAILED)" gpurun_out/r2b_pytest.log | head -24; tail -4 gpurun_out/r2b_pytest.log
 timeout 300 python __graft_entry__.py --smoke > gpurun_out/r2b_smoke.log 2>&1; echo "smoke exit=$?"; tail -3 gpurun_out/r2b_smoke.log
 timeout 900 python bench.py > gpurun_out/r2b_bench.json 2> gpurun_out/r2b_bench.err; echo "bench exit=$?"; cat gpurun_out/r2b_bench.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/r2b_bench_ref.json 2> gpurun_out/r2b_bench_ref.err; echo "bench ref exit=$?"; cat gpurun_out/r2b_bench_ref.json
