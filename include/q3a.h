@@ -130,8 +130,9 @@ int q3a_mel_batch_device(q3a_frontend* fe, const float* pcm_dev, const int64_t* 
  * (104-token windows); layer_norm_eps and n_window_infer are read from "audio.layer_norm_eps" /
  * "audio.n_window_infer" like the reference's loader does (gguf_loader.cpp:76-77), default 1e-5 / 800.
  * Every tensor the reference's graph uses must be present (all biases, ln_post, proj1/2): the reference treats them
- * as optional, this loader does not.  Q8_0 files: Linear weights stay Q8_0 blocks in device memory and are
- * dequantised inside the GEMM's producer (Q3A_Q8_DEQUANT_AT_LOAD=1 in the environment expands them at load instead). */
+ * as optional, this loader does not.  Q8_0 files: the Linear weights are expanded to the 16-bit operand type at load (d * q,
+ * rounded once); with Q3A_Q8_FUSED=1 in the environment they stay Q8_0 blocks in device memory and the GEMM's dequant
+ * warps expand them tile by tile -- the same bits, half the weight memory, about 1.6x the time. */
 int q3a_encoder_load(const char* gguf_path, int device, int operand_dtype, q3a_encoder** out);
 void q3a_encoder_free(q3a_encoder* enc);
 int q3a_encoder_get_hparams(const q3a_encoder* enc, q3a_hparams* out);

@@ -195,7 +195,9 @@ constexpr bool kDefaultAttnV2 = false;       // attention2.cu instead of attenti
                                              // (validated r2a: all 76 parity cases green, but 157 us against 133 us per
                                              //  layer on the bench shape -- DESIGN.md 4.4 -- so the first kernel stays default)
 constexpr bool kDefaultLnFold = true;        // LayerNorm folded into the GEMMs                Q3A_LN_FOLD / Q3A_NO_LN_FOLD
-constexpr bool kDefaultQ8Fused = true;       // Q8_0 weights dequantised inside the GEMM       Q3A_Q8_FUSED / Q3A_Q8_DEQUANT_AT_LOAD
+constexpr bool kDefaultQ8Fused = false;      // Q8_0 weights dequantised inside the GEMM       Q3A_Q8_FUSED / Q3A_Q8_DEQUANT_AT_LOAD
+                                             // (validated bit-identical, halves the weight arena, but 36.0 against 22.3 ms per
+                                             //  64 x 30 s and 3.6 against 1.9 ms for one clip -- DESIGN.md 4.6 -- so opt-in)
 constexpr bool kDefaultConvCbMajor = true;   // channel-block-major K order in conv2 / conv3   Q3A_CONV_CB_MAJOR / Q3A_CONV_TAP_MAJOR
 inline bool feature_enabled(const char* env_on, const char* env_off, bool dflt) {
     if (getenv(env_off)) return false;

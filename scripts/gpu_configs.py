@@ -40,11 +40,9 @@ w = synth.random_weights(shape, 0)
 q8_path = synth.write_gguf(os.path.join(tmp, "asr_q8.gguf"), shape, w, "q8_0")
 # row a12: Q8_0 weights resident in HBM and dequantised inside the GEMM, against expanding them at load (Q3A_Q8_DEQUANT_AT_LOAD):
 # weight-arena bytes, single-clip latency, 64-clip throughput
-for tag, env in (("fused", None), ("at_load", "1")):
-    if env:
-        os.environ["Q3A_Q8_DEQUANT_AT_LOAD"] = env
-    else:
-        os.environ.pop("Q3A_Q8_DEQUANT_AT_LOAD", None)
+for tag, env in (("fused", "Q3A_Q8_FUSED"), ("at_load", "Q3A_Q8_DEQUANT_AT_LOAD")):
+    os.environ.pop("Q3A_Q8_FUSED", None); os.environ.pop("Q3A_Q8_DEQUANT_AT_LOAD", None)
+    os.environ[env] = "1"
     enc = B.Encoder(q8_path, 0, B.OP_BF16)
     res[f"q8_{tag}_weight_bytes"] = enc.device_bytes()
     print(f"q8 {tag}: weight arena {enc.device_bytes() / 1e6:.1f} MB", flush=True)
@@ -54,7 +52,7 @@ for tag, env in (("fused", None), ("at_load", "1")):
         run("config3_q8_92s_full_attention", enc, fe, [92 * 16000] * 8, B.MODE_ASR)
         run("config3_q8_92s_cut_30s", enc, fe, [480000, 480000, 480000, 32000] * 8, B.MODE_ASR)
     enc.close()
-os.environ.pop("Q3A_Q8_DEQUANT_AT_LOAD", None)
+os.environ.pop("Q3A_Q8_DEQUANT_AT_LOAD", None); os.environ.pop("Q3A_Q8_FUSED", None)
 # config 5 (per-GPU share of the 10-h corpus at 8 GPUs = 4500 s): log-uniform 2-60 s utterances, ASR bf16
 enc = B.Encoder(synth.write_gguf(os.path.join(tmp, "asr_f16.gguf"), shape, w, "f16"), 0, B.OP_BF16)
 rng = np.random.default_rng(500)
