@@ -25,25 +25,6 @@ __device__ __forceinline__ void store8_f32(float* p, const float (&v)[8]) {
     *(reinterpret_cast<float4*>(p) + 1) = make_float4(v[4], v[5], v[6], v[7]);
 }
 
-// 32 column values of a chunk (bias, or the fold's c / s vectors), loaded ahead of the accumulators (EpiColState)
-struct Col32 { float v[32]; };
-__device__ __forceinline__ Col32 load_col32(const float* p, int n0, int nvalid) {
-    Col32 c;
-#pragma unroll
-    for (int g = 0; g < 4; ++g) {
-        if (p && g * 8 < nvalid) {
-            float t[8];
-            load8(p + n0 + g * 8, t);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) c.v[g * 8 + j] = t[j];
-        } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) c.v[g * 8 + j] = 0.0f;
-        }
-    }
-    return c;
-}
-
 // ---- staged epilogues (Linear layers): the kernel stores v through smem + TMA ---------------------
 // out[m][n] = act(acc + bias[n])  -> 16-bit operand for the next GEMM
 template <class OpT, bool kGelu>
@@ -52,14 +33,17 @@ struct EpiBiasActOp {
     static constexpr int kOutBytes = 2;
     const float* bias;
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
-    using ColState = Col32;
-    __device__ __forceinline__ ColState col_state(int n0, int nvalid) const { return load_col32(bias, n0, nvalid); }
-    __device__ __forceinline__ void apply(int, int, int nvalid, float (&v)[32], const ColState& cs) const {
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            if ((j & ~7) < nvalid) {
-                const float x = v[j] + cs.v[j];
-                v[j] = kGelu ? gelu_tanh(x) : x;
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float b[8];
+                if (bias) load8(bias + n0 + g * 8, b);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float x = v[g * 8 + j] + (bias ? b[j] : 0.0f);
+                    v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
+                }
             }
         }
     }
@@ -186,15 +170,18 @@ struct EpiLnFoldActOp {
     int rms;                 // 1: RMSNorm (no mean subtraction; the aligner's decoder, forced_aligner.cpp:1012-1013)
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
     __device__ __forceinline__ RowState row_state(int m) const { return ln_row_state(stats, n_part, M, inv_d, eps, rms, m); }
-    struct ColState { Col32 c, s; };
-    __device__ __forceinline__ ColState col_state(int n0, int nvalid) const { return ColState{load_col32(c, n0, nvalid), load_col32(s, n0, nvalid)}; }
-    __device__ __forceinline__ void apply(int, int, int nvalid, float (&v)[32], const RowState& rs, const ColState& cs) const {
-        const float nm = -rs.mean * rs.rstd;                      // y = rstd * acc + (c - mean * rstd * s)
+    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32], const RowState& rs) const {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-            if ((j & ~7) < nvalid) {
-                const float x = fmaf(rs.rstd, v[j], fmaf(nm, cs.s.v[j], cs.c.v[j]));
-                v[j] = kGelu ? gelu_tanh(x) : x;
+        for (int g = 0; g < 4; ++g) {
+            if (g * 8 < nvalid) {
+                float cc[8], ss[8];
+                load8(c + n0 + g * 8, cc);
+                load8(s + n0 + g * 8, ss);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float x = fmaf(rs.rstd, fmaf(-rs.mean, ss[j], v[g * 8 + j]), cc[j]);
+                    v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
+                }
             }
         }
     }

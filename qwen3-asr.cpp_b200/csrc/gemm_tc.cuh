@@ -67,20 +67,6 @@ using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes + 
 struct NoRowState {};
 template <class Epi, class = void> struct EpiRowState { using type = NoRowState; };
 template <class Epi> struct EpiRowState<Epi, decltype((void)sizeof(typename Epi::RowState))> { using type = typename Epi::RowState; };
-// per-column-chunk state (bias / fold vectors of the chunk's 32 columns): loaded BEFORE the accumulator load is waited
-// for, so that the L2 latency of those vectors runs under the tcgen05.ld instead of stalling the first FMA that uses them
-// (ncu source view of the FFN-up GEMM, profiles/r2b: the four FFMAs consuming the loaded vectors held 25 % of the samples)
-struct NoColState {};
-template <class Epi, class = void> struct EpiColState { using type = NoColState; };
-template <class Epi> struct EpiColState<Epi, decltype((void)sizeof(typename Epi::ColState))> { using type = typename Epi::ColState; };
-template <class Epi, class RS, class CS>
-__device__ __forceinline__ void epi_apply(const Epi& epi, int m, int n0, int nvalid, float (&v)[32], const RS& rs, const CS& cs) {
-    constexpr bool kRow = !std::is_same<RS, NoRowState>::value, kCol = !std::is_same<CS, NoColState>::value;
-    if constexpr (kRow && kCol) epi.apply(m, n0, nvalid, v, rs, cs);
-    else if constexpr (kRow) epi.apply(m, n0, nvalid, v, rs);
-    else if constexpr (kCol) epi.apply(m, n0, nvalid, v, cs);
-    else epi.apply(m, n0, nvalid, v);
-}
 
 // ---- A-operand coordinate policies (m128 = index of this CTA's 128-row block) -----------------
 // The producer and the MMA issuer walk the K blocks of a tile with a small iterator that is advanced
@@ -439,8 +425,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // chunk's store is still reading, so it goes out after the accumulator load and the functor, by which
                 // time that read has long finished and lane 0 does not hold up the warp's aligned tcgen05.ld.
                 if constexpr (kEpiBufs > 2) prefetch_next_residual();
-                typename EpiColState<Epilogue>::type cs{};
-                if constexpr (kStaged && !std::is_same<typename EpiColState<Epilogue>::type, NoColState>::value) cs = epi.col_state(n0, nvalid);
                 uint32_t r[32];
                 tc::tmem_ld_32x32b_x32(t_row + c * 32, r);
                 tc::tmem_ld_wait();
@@ -450,7 +434,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if constexpr (!kStaged) {
                     if (m < M) epi(m, n0, nvalid, v);
                 } else {
-                    epi_apply(epi, m, n0, nvalid, v, rs, cs);
+                    if constexpr (std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value) epi.apply(m, n0, nvalid, v);
+                    else epi.apply(m, n0, nvalid, v, rs);
                     if constexpr (kEpiBufs <= 2) prefetch_next_residual();
                     const int b = seq % kEpiBufs;
                     uint8_t* buf = my_bufs_gen + b * kBufBytes;
