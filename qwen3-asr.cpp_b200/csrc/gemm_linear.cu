@@ -57,25 +57,37 @@ int pick_block_n(int N) {
     return 128;
 }
 
-template <int BLOCK_N, int kFmt, class Epi>
-static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t stream) {
-    using S = GemmSmemFor<BLOCK_N, Epi>;
+template <int BLOCK_N, int kFmt, class Epi, int kEW>
+static int launch_linear_ew(const LinearArgs& a, const Epi& epi, cudaStream_t stream) {
+    using S = GemmSmemFor<BLOCK_N, Epi, false, kEW>;
     CUtensorMap ta, tb, tc_;
     Q3A_TRY(make_tmap_2d(&ta, a.a, (uint64_t)a.M, (uint64_t)a.K, (uint64_t)a.lda, kBlockM));
     Q3A_TRY(make_tmap_2d(&tb, a.w, (uint64_t)a.N, (uint64_t)a.K, (uint64_t)a.ldw, BLOCK_N / 2));
     Q3A_TRY(make_tmap_tile32(&tc_, a.out, Epi::kOutBytes, (uint64_t)a.M, (uint64_t)a.N, (uint64_t)a.ldc));
     CUtensorMap tc2 = tc_;
     if (EpiDual<Epi>::value) Q3A_TRY(make_tmap_tile32(&tc2, a.out16, 2, (uint64_t)a.M, (uint64_t)a.N, (uint64_t)a.ldc));
-    auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderLinear, Epi>;
+    auto kern = gemm_tc_kernel<BLOCK_N, kFmt, LoaderLinear, Epi, false, kEW>;
+    constexpr int kThreads = 128 + 32 * kEW;
     int pairs = 0;
-    Q3A_TRY(gemm_prepare(kern, S::kTotal, &pairs));
+    Q3A_TRY(gemm_prepare_impl(reinterpret_cast<const void*>(kern), S::kTotal, kThreads, &pairs));
     LoaderLinear loader{ceil_div(a.K, kBlockK)};
     const int tiles = ceil_div(a.M, 2 * kBlockM) * ceil_div(a.N, BLOCK_N);
     const int grid = 2 * (tiles < pairs ? tiles : pairs);
-    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kGemmThreads), S::kTotal, stream, ta, tb, tc_, tc2, a.M, a.N, loader, epi, Q8Scales{}));
+    Q3A_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), S::kTotal, stream, ta, tb, tc_, tc2, a.M, a.N, loader, epi, Q8Scales{}));
     ++g_launch_counter;
     Q3A_CUDA(cudaGetLastError());
     return Q3A_OK;
+}
+
+// Q3A_EPI_WARPS=8: A/B switch for the 12-warp epilogue of the 16-bit-output GEMMs
+static int epi_warps_16bit() { const char* e = getenv("Q3A_EPI_WARPS"); return e && atoi(e) == 8 ? 8 : 12; }
+
+template <int BLOCK_N, int kFmt, class Epi>
+static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t stream) {
+    if constexpr (Epi::kStaged && Epi::kOutBytes == 2) {
+        if (epi_warps_16bit() == 12) return launch_linear_ew<BLOCK_N, kFmt, Epi, 12>(a, epi, stream);
+    }
+    return launch_linear_ew<BLOCK_N, kFmt, Epi, 8>(a, epi, stream);
 }
 
 // Q8_0 weights, dequantised inside the kernel (gemm_tc.cuh, kWq8): the W tensor map covers the int8 plane

@@ -39,18 +39,18 @@ constexpr int kBlockK = 64;                 // 64 x 16-bit = 128 B = one swizzle
 constexpr int kUmmaK = 16;
 constexpr int kGemmThreads = 384;           // 4 control warps + 8 epilogue warps
 constexpr int kDequantWarps = 4;            // Q8_0 weight path: + 4 warps that expand int8 blocks into the operand stage
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 8;                // default; the kernel takes the count as a template parameter (kEW: 8 or 12)
 constexpr int kTmemCols = 512;              // two accumulator buffers of up to 256 columns
 constexpr int kSmemLimit = 232448;          // 227 KB opt-in maximum per CTA
 
 // kEpiBufBytes: bytes of one epilogue staging buffer set (32 rows; a dual-output epilogue stages the f32 chunk and its
 // 16-bit copy), kEpiBufs: buffer sets per epilogue warp
-template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs, bool kWq8 = false> struct GemmSmem {
+template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs, bool kWq8 = false, int kEW = kEpiWarps> struct GemmSmem {
     static constexpr int kABytes = kBlockM * kBlockK * 2;              // 16 KB
     static constexpr int kBBytes = (BLOCK_N / 2) * kBlockK * 2;        // this CTA's half of the W tile
     static constexpr int kRawBytes = kWq8 ? (BLOCK_N / 2) * kBlockK : 0;   // the same half as int8 (Q8_0 weights)
     static constexpr int kStageBytes = kABytes + kBBytes + kRawBytes;
-    static constexpr int kEpiBytes = kEpiWarps * kEpiBufs * kEpiBufBytes;
+    static constexpr int kEpiBytes = kEW * kEpiBufs * kEpiBufBytes;
     static constexpr int kBarrierBytes = 512;
     static constexpr int kAvail = kSmemLimit - 1024 - kBarrierBytes - kEpiBytes;
     static constexpr int kStages = kAvail / kStageBytes > 6 ? 6 : kAvail / kStageBytes;
@@ -60,9 +60,9 @@ template <int BLOCK_N, int kEpiBufBytes, int kEpiBufs, bool kWq8 = false> struct
 };
 // the shared-memory plan of a (BLOCK_N, epilogue) instantiation, for kernel and host alike
 template <class Epi> struct EpiDual { static constexpr bool value = false; };     // specialised by dual-output epilogues
-template <int BLOCK_N, class Epi, bool kWq8 = false>
+template <int BLOCK_N, class Epi, bool kWq8 = false, int kEW = kEpiWarps>
 using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes + (EpiDual<Epi>::value ? 32 * 32 * 2 : 0) : 0,
-                             Epi::kStaged ? (Epi::kResidual && !EpiDual<Epi>::value ? 3 : 2) : 0, kWq8>;
+                             Epi::kStaged ? (Epi::kResidual && !EpiDual<Epi>::value ? 3 : 2) : 0, kWq8, kEW>;
 // per-row state an epilogue may carry across the column chunks of a tile (LayerNorm-folded epilogues keep mean / rstd)
 struct NoRowState {};
 template <class Epi, class = void> struct EpiRowState { using type = NoRowState; };
@@ -148,8 +148,10 @@ struct Q8Scales {
 //   direct   struct E { static constexpr bool kStaged = false;
 //                       __device__ void operator()(int m, int n0, int nvalid, const float (&acc)[32]) const; }
 //            called for rows m < M; only the first nvalid (multiple of 8) columns belong to the output.
-template <int BLOCK_N, int kFmt, class Loader, class Epilogue, bool kWq8 = false>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads + (kWq8 ? 32 * kDequantWarps : 0), 1)
+// kEW epilogue warps: 8 (two per TMEM lane quadrant) or 12 (three).  The 16-bit-output GEMMs with K = 896 are paced by
+// their epilogue (FFN-up: 65 % tensor-active with 8 warps); a third warp per quadrant hides more of its latency.
+template <int BLOCK_N, int kFmt, class Loader, class Epilogue, bool kWq8 = false, int kEW = kEpiWarps>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128 + 32 * kEW + (kWq8 ? 32 * kDequantWarps : 0), 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                const __grid_constant__ CUtensorMap tmap_c, const __grid_constant__ CUtensorMap tmap_c2, int M, int N,
                Loader loader, Epilogue epi, Q8Scales q8 = Q8Scales{}) {
@@ -166,8 +168,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     // waits for the store of chunk i-1 to have READ its buffer (lane 0 only, ~100 clk, under the other lanes' tcgen05.ld) --
     // so that the stage ring keeps its depth.
     constexpr int kEpiBufs = kStaged ? (kResidual && !kDual ? 3 : 2) : 0;
-    using S = GemmSmemFor<BLOCK_N, Epilogue, kWq8>;
+    using S = GemmSmemFor<BLOCK_N, Epilogue, kWq8, kEW>;
     constexpr int kStages = S::kStages;
+    constexpr int kEpiPerQuad = kEW / 4;                                // epilogue warps sharing a TMEM lane quadrant
+    static_assert(kEW == 8 || kEW == 12, "8 or 12 epilogue warps");
+    static_assert(!EpiDual<Epilogue>::value || kEW == 8, "the dual-output statistics layout assumes two warps per quadrant");
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "BLOCK_N must be a multiple of 16, at most 256");
     static_assert(!kStaged || BLOCK_N % 32 == 0, "staged epilogues store whole 32-column chunks");
     static_assert(!kResidual || kOutBytes == 4, "the residual stream is fp32");
@@ -183,8 +188,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 2 + s); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 4);
     auto res_bar = [&](int w, int b) { return bar_base + 8u * (2 * kStages + 5 + w * 3 + b); };   // 24 barriers
-    auto raw_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 5 + 24 + s); };             // Q8 raw ring
-    static_assert(8 * (2 * 6 + 5 + 24 + 6) <= S::kBarrierBytes, "barrier block too small");
+    auto raw_bar = [&](int s) { return bar_base + 8u * (2 * kStages + 5 + 3 * kEW + s); };        // Q8 raw ring
+    static_assert(8 * (2 * 6 + 5 + 3 * kEW + 6) <= S::kBarrierBytes, "barrier block too small");
     volatile uint32_t* tmem_slot_ptr =
         reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * S::kStageBytes + S::kEpiBytes + 8 * (2 * kStages + 4));
 
@@ -208,8 +213,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             tc::mbar_init(full_bar(s), kWq8 ? 1 + 2 * kDequantWarps : 1); tc::mbar_init(empty_bar(s), 1);
             if (kWq8) tc::mbar_init(raw_bar(s), 1);
         }
-        for (int s = 0; s < 2; ++s) { tc::mbar_init(tfull_bar(s), 1); tc::mbar_init(tempty_bar(s), 2 * kEpiWarps); }
-        for (int w = 0; w < kEpiWarps; ++w)
+        for (int s = 0; s < 2; ++s) { tc::mbar_init(tfull_bar(s), 1); tc::mbar_init(tempty_bar(s), 2 * kEW); }
+        for (int w = 0; w < kEW; ++w)
             for (int b = 0; b < 3; ++b) tc::mbar_init(res_bar(w, b), 1);
         tc::fence_barrier_init();
     }
@@ -292,7 +297,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 __syncwarp();
             }
         }
-    } else if (kWq8 && warp >= 4 + kEpiWarps) {
+    } else if (kWq8 && warp >= 4 + kEW) {
         // ===================== Q8_0 dequantisation (both CTAs): raw int8 tile -> swizzled 16-bit operand tile =========
         // One W row per thread: 64 int8 (4 x LDS.128, chunk order rotated by row so that a quarter-warp hits eight
         // different 16-byte bank groups) -> value = d * q exactly as ggml defines Q8_0 (one f32 rounding-free product:
@@ -300,7 +305,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
         // rounded once to the operand type, the same value the dequantise-at-load path stores -> 8 x STS.128 into the
         // 128-byte-swizzled K-major layout (conflict-free by construction).
         using OpT = typename std::conditional<kFmt == 1, __nv_bfloat16, __half>::type;
-        const int r = (warp - 4 - kEpiWarps) * 32 + lane;                  // row of this CTA's half tile
+        const int r = (warp - 4 - kEW) * 32 + lane;                  // row of this CTA's half tile
         const bool has_row = r < BLOCK_N / 2;
         const uint32_t full_leader0 = tc::mapa(full_bar(0), 0);
         int s = 0;
@@ -351,11 +356,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (++s == kStages) { s = 0; ph ^= 1; }
             }
         }
-    } else if (warp >= 4 && warp < 4 + kEpiWarps) {
+    } else if (warp >= 4 && warp < 4 + kEW) {
         // ===================== epilogue (both CTAs) =====================
         const int ew = warp - 4;
         const int q = warp & 3;                       // TMEM lane quadrant this warp may read
-        const int hf = ew >> 2;                       // which half of the 32-column chunks
+        const int hf = ew >> 2;                       // which share of the 32-column chunks (0 .. kEpiPerQuad-1)
         const uint32_t tempty_leader0 = tc::mapa(tempty_bar(0), 0), tempty_leader1 = tc::mapa(tempty_bar(1), 0);
         const uint32_t my_bufs = epi_base + ew * kEpiBufs * kBufBytes;
         uint8_t* my_bufs_gen = smem_gen + kStages * S::kStageBytes + ew * kEpiBufs * kBufBytes;
@@ -394,7 +399,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 if (lane == 0 && nt < num_tiles && epi.prefetch) {
                     const int m_n = nt / n_blocks, n_n = nt - m_n * n_blocks;
                     const int nch_n = chunks_of(n_n);
-                    for (int c = hf; c < nch_n; c += 2)
+                    for (int c = hf; c < nch_n; c += kEpiPerQuad)
                         tc::tma_prefetch_2d(&tmap_c, n_n * BLOCK_N + c * 32, (2 * m_n + (int)rank) * kBlockM + q * 32);
                 }
             }
@@ -407,13 +412,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if constexpr (!std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value) rs = epi.row_state(m);
             float st_sum = 0.0f, st_sq = 0.0f;             // dual output: this warp's share of the row's statistics
 #pragma unroll 1
-            for (int c = hf; c < nch; c += 2) {
+            for (int c = hf; c < nch; c += kEpiPerQuad) {
                 const int n0 = n_blk * BLOCK_N + c * 32;
                 const int nvalid = min(32, min(BLOCK_N - c * 32, N - n0));
                 auto prefetch_next_residual = [&]() {
                     if (kResidual && lane == 0) {
                         // next chunk of this warp: same tile, or the first chunk of its next tile
-                        int nt = tile, nc = c + 2;
+                        int nt = tile, nc = c + kEpiPerQuad;
                         if (nc >= nch) { nt = tile_with_chunk(tile + num_pairs); nc = hf; }
                         if (nt < num_tiles) {
                             tc::bulk_wait_group_read<(kEpiBufs > 2 ? kEpiBufs - 2 : 0)>();   // the store that last used that buffer has read it
