@@ -89,11 +89,21 @@ def test_shim_decoder_consumes_encoder_features(lib, harness, tmp_path):
                       n_heads=shape.n_heads, variant="aligner")
     n = feats.shape[0] + 12
     tokens = np.array([(i * 7 + 3) % dshape.vocab for i in range(n)], dtype=np.int32)
-    want = DO.forward(tokens, dw, dshape, feats, 1)
-    got = np.fromfile(tmp_path / "logits.f32", dtype=np.float32).reshape(want.shape)
-    cos = float((got * want).sum() / (np.linalg.norm(got) * np.linalg.norm(want)))
-    rel = float(np.abs(got - want).max() / np.abs(want).max())
-    assert cos >= 0.999 and rel <= 1e-2, (cos, rel)
+    got = np.fromfile(tmp_path / "logits.f32", dtype=np.float32)
+
+    def compare(want):
+        g = got.reshape(want.shape)
+        return (float((g * want).sum() / (np.linalg.norm(g) * np.linalg.norm(want))),
+                float(np.abs(g - want).max() / np.abs(want).max()))
+    # (1) the decoder stage on its own: the oracle fed the features the encoder shim actually produced -- the per-stage
+    #     bf16 bound (1e-2 of the peak), and the proof that forward_decoder injected those features at audio_start
+    got_feats = np.fromfile(tmp_path / "feat.f32", dtype=np.float32).reshape(feats.shape)
+    cos, rel = compare(DO.forward(tokens, dw, dshape, got_feats.astype(np.float64), 1))
+    assert cos >= 0.9999 and rel <= 1e-2, (cos, rel)
+    # (2) the whole chain against the two f64 restatements chained: two bf16 towers in series, each within 1e-2 of its own
+    #     oracle (this file and test_decoder_gpu.py), so the chain is held to the sum of the two bounds
+    cos, rel = compare(DO.forward(tokens, dw, dshape, feats, 1))
+    assert cos >= 0.9999 and rel <= 2e-2, (cos, rel)
 
 
 @pytest.fixture(scope="module")
