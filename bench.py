@@ -462,6 +462,45 @@ def run_ours(args):
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     e2e_parts_value = audio_s / float(dt.item())
 
+    # ---- host link probe: every rank moves one step's worth of PCM up and features down at the same moment, with no
+    #      kernels running -- the copy time an e2e step has to hide, and the evidence for what bounds e2e at N > 1
+    #      (all ranks share the host's memory controllers and PCIe root ports)
+    link = None
+    if not args.no_link_probe:
+        cs_in, cs_out = torch.cuda.Stream(), torch.cuda.Stream()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        res = []
+        for both in (False, True):                    # each direction alone, then both at once (what the pipeline does)
+            barrier()
+            reps = 4
+            with torch.cuda.stream(cs_in):
+                ev[0].record()
+                for r in range(reps):
+                    dev_sets[r & 1].copy_(sets[r & 1], non_blocking=True)
+                ev[1].record()
+            if not both:
+                torch.cuda.synchronize()
+                barrier()
+            with torch.cuda.stream(cs_out):
+                ev[2].record()
+                for r in range(reps):
+                    out_blocks[r & 1].copy_(out_dev, non_blocking=True)
+                ev[3].record()
+            torch.cuda.synchronize()
+            res += [reps * sets[0].numel() * 4 / ev[0].elapsed_time(ev[1]) / 1e6, reps * out_dev.numel() * 4 / ev[2].elapsed_time(ev[3]) / 1e6]
+        lt = torch.tensor(res, device="cuda")
+        lo, hi = lt.clone(), lt.clone()
+        if world > 1:
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        keys = ("h2d_alone", "d2h_alone", "h2d_with_d2h", "d2h_with_h2d")
+        link = {"unit": "GB/s per rank, all ranks copying at once, pinned host memory, no kernels running",
+                "min_over_ranks": {k: round(float(v), 2) for k, v in zip(keys, lo.tolist())},
+                "max_over_ranks": {k: round(float(v), 2) for k, v in zip(keys, hi.tolist())}}
+        h2d_ms = sets[0].numel() * 4 / (link["min_over_ranks"]["h2d_with_d2h"] * 1e6)
+        d2h_ms = out_dev.numel() * 4 / (link["min_over_ranks"]["d2h_with_h2d"] * 1e6)
+        link["copy_ms_per_step"] = {"h2d": round(h2d_ms, 3), "d2h": round(d2h_ms, 3)}
+
     # ---- the timed device-resident call is checked, not just timed: its output must equal, bit for bit, what the
     #      (tested) host-pointer call returns for the same input set (batch-invariant kernels, same code underneath)
     step_e2e(0)
@@ -543,7 +582,8 @@ def run_ours(args):
                 "api": "q3a_encode_pcm_submit + q3a_encode_wait (pinned host PCM -> pinned host features), two calls in flight",
                 "with_intra_call_parts_value": e2e_parts_value,
                 "synchronous_call_value": e2e_sync_value,
-                "synchronous_api": "q3a_encode_pcm_batch, one call at a time"},
+                "synchronous_api": "q3a_encode_pcm_batch, one call at a time",
+                "host_link": link},
         "gpu_launches": launches0,
         "ranks_share_gpus": emulated,
         "value_checked": value_checked, "value_check": {"against": "q3a_encode_pcm_batch on the same 64 clips (host result)",
@@ -588,6 +628,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~20 s CPU baseline leg (profiling runs)")
     ap.add_argument("--no-corpus", action="store_true", help="skip the sharded 10-h corpus leg (profiling runs)")
+    ap.add_argument("--no-link-probe", action="store_true", help="skip the host<->device copy-rate probe of the e2e leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     # stdout carries exactly one JSON line: libraries that print there (NCCL's version banner) go to stderr

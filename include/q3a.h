@@ -254,8 +254,9 @@ int q3a_test_attention_v(const void* qkv_dev, void* out_dev, int T, int H, const
                          int operand_dtype, int version, void* stream);
 
 /* Development probe (csrc/probe.cu): cycles that n_mma back-to-back tcgen05.mma (cta_group::1, M = 128, K = 16, bf16) of
- * width N take on each of `grid` CTAs, A from shared memory (0) or TMEM (1), accumulating into one TMEM region or
- * alternating between two; cycles_out_dev: device int64[grid]. */
+ * width N take on each of `grid` CTAs, A from shared memory (a_from_tmem bit 0 clear) or TMEM (bit 0 set), with M = 64
+ * instead of 128 when bit 1 is set, accumulating into one TMEM region or alternating between two; cycles_out_dev:
+ * device int64[grid]. */
 int q3a_probe_mma_rate(int N, int a_from_tmem, int n_mma, int alternate, int k_steps_per_commit, int grid,
                        long long* cycles_out_dev, void* stream);
 

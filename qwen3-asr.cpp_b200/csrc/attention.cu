@@ -6,8 +6,9 @@
 // utterance for the ASR encoder (no mask), 104-token windows for the aligner.  Scores are never
 // written to HBM.
 //
-// One CTA (128 threads, one query row per thread) = one (128-query tile, head); keys go in blocks of KT = 64
-// (three CTAs per SM; KT = 128 with two CTAs per SM is kept behind Q3A_ATTN_KT=128).
+// One CTA (128 threads, one query row per thread) = one (128-query tile, head); keys go in blocks of KT = 64 (three CTAs
+// per SM) for segments below 1024 tokens and KT = 128 (two CTAs per SM) from there on -- chosen per SEGMENT, so that a
+// clip's result does not depend on what it is batched with (attention_key_block; Q3A_ATTN_KT=64|128 forces one).
 // Per key block j:
 //   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,KT)
 //   S_j -> registers         tcgen05.ld.x32 back to back, one wait
@@ -71,7 +72,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + kBarOff + 56);
 
     const int tid = threadIdx.x, warp = tid >> 5;
-    const AttnTile t = tiles[blockIdx.x];
+    const AttnTile t = tiles[blockIdx.x];                  // (the table is a host upload, not the previous kernel's output)
+    if (t.pad != kKT) return;                              // a mixed launch: this tile belongs to the other block size
     const int head = blockIdx.y;
     const int seg_len = t.seg_end - t.seg_start;
     const int nkv = (seg_len + kKT - 1) / kKT;
@@ -314,11 +316,24 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     if (warp == 0) tc::tmem_dealloc<kAttnTmemCols>(tmem);
 }
 
-void attention_tiles(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& tiles) {
+// Keys per block for a segment of this length.  Measured: 128 wins from ~1200 tokens (112 vs 116 us at
+// 1196, 639 vs 662 us at 4096), 64 below (133 vs 151 us at 390, 78 vs 92 us on 104-token windows).
+int attention_key_block(int seg_len) {
+    static const int forced = [] { const char* e = getenv("Q3A_ATTN_KT"); const int v = e ? atoi(e) : 0; return v == 64 || v == 128 ? v : 0; }();
+    if (forced) return forced;
+    return seg_len >= 1024 ? 128 : 64;
+}
+
+int attention_tiles(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& tiles) {
     tiles.clear();
-    for (int s = 0; s < n_seg; ++s)
+    int mask = 0;
+    for (int s = 0; s < n_seg; ++s) {
+        const int kt = attention_key_block(cu_seqlens[s + 1] - cu_seqlens[s]);
+        if (cu_seqlens[s + 1] > cu_seqlens[s]) mask |= kt == 128 ? 2 : 1;
         for (int q0 = cu_seqlens[s]; q0 < cu_seqlens[s + 1]; q0 += kQT)
-            tiles.push_back(AttnTile{q0, cu_seqlens[s], cu_seqlens[s + 1], 0});
+            tiles.push_back(AttnTile{q0, cu_seqlens[s], cu_seqlens[s + 1], kt});
+    }
+    return mask;
 }
 
 double attention_flops(const int* cu_seqlens, int n_seg, int n_heads) {
@@ -346,16 +361,19 @@ static int attention_launch_kt(const void* qkv, void* out, int T, int d, const A
 }
 
 int attention_launch(const void* qkv, void* out, int T, int n_heads, const AttnTile* tiles_dev, int n_tiles, int fmt,
-                     cudaStream_t stream) {
+                     int kt_mask, cudaStream_t stream) {
     if (n_tiles == 0 || T == 0) return Q3A_OK;
     const int d = n_heads * kHd;
-    static const int kt = [] { const char* e = getenv("Q3A_ATTN_KT"); return e && atoi(e) == 128 ? 128 : 64; }();
-    if (kt == 128) {
-        if (fmt == OP_F16) return attention_launch_kt<__half, 128>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
-        return attention_launch_kt<__nv_bfloat16, 128>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
+    // one launch per block size present; in a mixed launch the CTAs of the other size's tiles leave at once
+    if (kt_mask & 1) {
+        if (fmt == OP_F16) Q3A_TRY((attention_launch_kt<__half, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream)));
+        else Q3A_TRY((attention_launch_kt<__nv_bfloat16, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream)));
     }
-    if (fmt == OP_F16) return attention_launch_kt<__half, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
-    return attention_launch_kt<__nv_bfloat16, 64>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream);
+    if (kt_mask & 2) {
+        if (fmt == OP_F16) Q3A_TRY((attention_launch_kt<__half, 128>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream)));
+        else Q3A_TRY((attention_launch_kt<__nv_bfloat16, 128>(qkv, out, T, d, tiles_dev, n_tiles, n_heads, stream)));
+    }
+    return Q3A_OK;
 }
 
 int attention_version() {
@@ -374,7 +392,8 @@ extern "C" int q3a_test_attention_v(const void* qkv_dev, void* out_dev, int T, i
     if (version == 0) version = attention_version();
     if (version != 1 && version != 2) { set_error("test_attention: version must be 0 (default), 1 or 2"); return Q3A_ERR_ARG; }
     std::vector<AttnTile> tiles;
-    if (version == 1) attention_tiles(cu_seqlens, n_seg, tiles);
+    int kt_mask = 0;
+    if (version == 1) kt_mask = attention_tiles(cu_seqlens, n_seg, tiles);
     else attention2_items(cu_seqlens, n_seg, tiles);
     if (tiles.empty()) return Q3A_OK;
     static DevBuf d_tiles_buf;                       // test-only entry point: grow-only scratch, never freed
@@ -386,7 +405,7 @@ extern "C" int q3a_test_attention_v(const void* qkv_dev, void* out_dev, int T, i
     int rc = Q3A_OK;
     if (e != cudaSuccess) { set_error(cudaGetErrorString(e)); rc = Q3A_ERR_CUDA; }
     if (rc == Q3A_OK)
-        rc = version == 1 ? attention_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, st)
+        rc = version == 1 ? attention_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, kt_mask, st)
                           : attention2_launch(qkv_dev, out_dev, T, H, d_tiles, (int)tiles.size(), operand_dtype, st);
     if (!st) cudaStreamSynchronize(st);               // with a caller's stream the call stays asynchronous
     return rc;

@@ -378,7 +378,12 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         const int sg0 = utt_seg0[ua], sg1 = utt_seg0[ub];
         const int tile0 = seg_tile0[sg0], n_tiles = seg_tile0[sg1] - tile0;
         double attn_fl = 0.0;
-        for (int sgi = sg0; sgi < sg1; ++sgi) { const double len = cu[sgi + 1] - cu[sgi]; attn_fl += attn_fl_per_tile_unit * len * len; }
+        int kt_mask = 0;                                  // key-block sizes among this launch's segments (v1 kernel)
+        for (int sgi = sg0; sgi < sg1; ++sgi) {
+            const double len = cu[sgi + 1] - cu[sgi];
+            attn_fl += attn_fl_per_tile_unit * len * len;
+            if (len > 0) kt_mask |= attention_key_block((int)len) == 128 ? 2 : 1;
+        }
         float* xr = x + (size_t)t0 * d;
         void* hr = rows16(h, d, t0);
         void* attr = rows16(e->att.p, d, t0);
@@ -392,7 +397,7 @@ static int encode_core(q3a_encoder* e, const float* mel_dev, const int64_t* mel_
         float2* str = fold ? e->stats.as<float2>() + (size_t)t0 * n_part : nullptr;
         auto attention = [&]() -> int {
             const int sp = prof.begin(SP_ATTN);
-            if (attn_v == 1) Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
+            if (attn_v == 1) Q3A_TRY(attention_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, kt_mask, st));
             else Q3A_TRY(attention2_launch(e->qkv.p, e->att.p, T, H, d_tiles + tile0, n_tiles, fmt, st));
             prof.end(sp);
             e->tm.attention_flops += attn_fl; ++e->tm.attention_launches;

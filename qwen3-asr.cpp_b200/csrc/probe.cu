@@ -23,8 +23,10 @@ mma_rate_kernel(int N, int a_from_tmem, int n_mma, int alternate, int k_steps_pe
     __syncthreads();
     tc::fence_after_sync();
     const uint32_t tmem = *slot_ptr;
+    const int M = (a_from_tmem & 2) ? 64 : 128;           // bit 1 of the operand-source argument: the M = 64 shape
+    a_from_tmem &= 1;
     if (warp == 0) {
-        const uint32_t idesc = tc::make_idesc(1, 128, N, 0, 0);
+        const uint32_t idesc = tc::make_idesc(1, M, N, 0, 0);
         const uint64_t a = tc::smem_desc_kmajor_sw128(base), b = tc::smem_desc_kmajor_sw128(base + 16384);
         uint32_t ph = 0;
         long long t0 = 0, t1 = 0;
@@ -62,7 +64,7 @@ extern "C" int q3a_probe_mma_rate(int N, int a_from_tmem, int n_mma, int alterna
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) { set_error("no CUDA device"); return Q3A_ERR_CUDA; }
     Q3A_TRY(use_device(dev));
-    if (N < 16 || N > 256 || N % 16 || n_mma <= 0 || grid <= 0 || k_steps_per_commit <= 0 || !cycles_out_dev || (alternate && N > 192)) {
+    if (a_from_tmem < 0 || a_from_tmem > 3 || ((a_from_tmem & 2) && N % 8) || N < 16 || N > 256 || (!(a_from_tmem & 2) && N % 16) || n_mma <= 0 || grid <= 0 || k_steps_per_commit <= 0 || !cycles_out_dev || (alternate && N > 192)) {
         set_error("probe_mma_rate: bad argument"); return Q3A_ERR_ARG;
     }
     const int smem = 16384 + 32768 + 64 + 1024;

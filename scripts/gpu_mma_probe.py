@@ -10,6 +10,12 @@ lib = B.load()
 n = 4096
 for grid in (1, 148):
     out = torch.zeros(grid, dtype=torch.int64, device="cuda")
+    for N in (16, 64, 128, 256):                      # M = 64: what a remainder tile of <= 64 query rows would cost
+        for ts in (0, 1):
+            B.check(lib.q3a_probe_mma_rate(N, ts | 2, n, 0, 4, grid, out.data_ptr(), None))
+            torch.cuda.synchronize()
+            per = float(out.float().median()) / n
+            print(f"grid {grid:3d} M=64 A from {'TMEM' if ts else 'smem'} N={N:3d}: {per:6.1f} clk/MMA", flush=True)
     for ts in (0, 1):
         for alt in (0, 1):
             for N in (16, 32, 64, 112, 128, 192, 256):

@@ -62,3 +62,27 @@ def test_attention_matches_fp32_softmax(lib, opd, tol, H, cu, version):
     assert torch.isfinite(out.float()).all()
     # P and the output are rounded to the 16-bit operand type: 2^-8 (bf16) / 2^-11 (f16) relative
     assert (out.float() - want).abs().max().item() <= tol
+
+
+@pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
+def test_attention_key_block_is_chosen_per_segment(lib, opd):
+    """The 64- / 128-key block size follows the segment's own length (128 from 1024 tokens, attention.cu
+    attention_key_block), never the batch: a clip's rows are bit-identical whether it runs alone (one launch) or packed
+    between longer and shorter clips (two launches, one per block size)."""
+    H = 3
+    torch.manual_seed(77)
+    lens = [390, 1500, 104, 1024, 1023]
+    parts = [(torch.randn(n, 3 * H * 64, device="cuda") * 1.5).to(DT[opd]) for n in lens]
+    cu = [0]
+    for n in lens:
+        cu.append(cu[-1] + n)
+    qkv = torch.cat(parts)
+    out = torch.full((cu[-1], H * 64), float("nan"), device="cuda").to(DT[opd])
+    B.test_attention(qkv, out, H, cu, opd, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(out.float()).all()
+    for i, n in enumerate(lens):
+        alone = torch.full((n, H * 64), float("nan"), device="cuda").to(DT[opd])
+        B.test_attention(parts[i], alone, H, [0, n], opd, 1)
+        torch.cuda.synchronize()
+        assert torch.equal(alone, out[cu[i]:cu[i + 1]]), f"segment {i} ({n} tokens) depends on its batch"
