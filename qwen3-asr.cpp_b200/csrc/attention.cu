@@ -7,7 +7,7 @@
 // written to HBM.
 //
 // One CTA (128 threads, one query row per thread) = one (128-query tile, head); keys go in blocks of KT = 64 (three CTAs
-// per SM) for segments below 1024 tokens and KT = 128 (two CTAs per SM) from there on -- chosen per SEGMENT, so that a
+// per SM) for segments below 2048 tokens and KT = 128 (two CTAs per SM) from there on -- chosen per SEGMENT, so that a
 // clip's result does not depend on what it is batched with (attention_key_block; Q3A_ATTN_KT=64|128 forces one).
 // Per key block j:
 //   S_j = Q K_j^T            tcgen05.mma into TMEM columns [0,KT)
@@ -316,12 +316,13 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     if (warp == 0) tc::tmem_dealloc<kAttnTmemCols>(tmem);
 }
 
-// Keys per block for a segment of this length.  Measured: 128 wins from ~1200 tokens (112 vs 116 us at
-// 1196, 639 vs 662 us at 4096), 64 below (133 vs 151 us at 390, 78 vs 92 us on 104-token windows).
+// Keys per block for a segment of this length.  Measured at 24 960 tokens x 14 heads per launch (visit r2f):
+// 128 wins from 2048 tokens (347 vs 355 us; 639 vs 662 us at 4096), is level at 1024 (200 vs 201 us) and loses below
+// and at 1196 (244 vs 234 us; 152 vs 135 us at 390; 92 vs 78 us on 104-token windows).
 int attention_key_block(int seg_len) {
     static const int forced = [] { const char* e = getenv("Q3A_ATTN_KT"); const int v = e ? atoi(e) : 0; return v == 64 || v == 128 ? v : 0; }();
     if (forced) return forced;
-    return seg_len >= 1024 ? 128 : 64;
+    return seg_len >= 2048 ? 128 : 64;
 }
 
 int attention_tiles(const int* cu_seqlens, int n_seg, std::vector<AttnTile>& tiles) {

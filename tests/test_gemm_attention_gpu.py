@@ -66,12 +66,12 @@ def test_attention_matches_fp32_softmax(lib, opd, tol, H, cu, version):
 
 @pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
 def test_attention_key_block_is_chosen_per_segment(lib, opd):
-    """The 64- / 128-key block size follows the segment's own length (128 from 1024 tokens, attention.cu
+    """The 64- / 128-key block size follows the segment's own length (128 from 2048 tokens, attention.cu
     attention_key_block), never the batch: a clip's rows are bit-identical whether it runs alone (one launch) or packed
     between longer and shorter clips (two launches, one per block size)."""
     H = 3
     torch.manual_seed(77)
-    lens = [390, 1500, 104, 1024, 1023]
+    lens = [390, 2500, 104, 2048, 2047]
     parts = [(torch.randn(n, 3 * H * 64, device="cuda") * 1.5).to(DT[opd]) for n in lens]
     cu = [0]
     for n in lens:
