@@ -64,8 +64,33 @@ class ClockSampler:
 
     def __init__(self, index: int):
         self.index, self.rows, self.stop_ev, self.th = index, [], threading.Event(), None
+        self.source = "nvidia-smi, 0.1-s period"
+
+    def _run_nvml(self) -> bool:
+        """NVML in-process (a sample every 5 ms: a 10-step timed region is only ~0.2 s long); False when unavailable"""
+        try:
+            import pynvml as N
+            N.nvmlInit()
+            h = N.nvmlDeviceGetHandleByIndex(self.index)
+            mx = N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM)
+            get_reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or N.nvmlDeviceGetCurrentClocksThrottleReasons
+            N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM); get_reasons(h)
+            self.source = "nvml, 5-ms period"
+        except Exception:
+            return False
+        bits = ((0x8, "hw_slowdown"), (0x40, "hw_thermal_slowdown"), (0x20, "sw_thermal_slowdown"), (0x4, "sw_power_cap"))
+        while not self.stop_ev.is_set():
+            try:
+                sm, r = N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM), int(get_reasons(h))
+                self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b, _ in bits])
+            except Exception:
+                pass
+            self.stop_ev.wait(0.005)
+        return True
 
     def _run(self):
+        if self._run_nvml():
+            return
         while not self.stop_ev.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
@@ -95,7 +120,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+                "samples": len(sm), "sampler": self.source}
 
 
 def ensure_gguf(tmpdir: str, ftype: str = "f16") -> str:
