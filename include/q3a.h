@@ -249,7 +249,8 @@ int q3a_test_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, f
 int q3a_test_attention(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
                        int operand_dtype, void* stream);
 /* same with the kernel generation chosen explicitly: 1 = one query tile per CTA (attention.cu), 2 = persistent CTAs with
- * two ping-ponging query tiles (attention2.cu, what the encoder runs), 0 = the encoder's choice. */
+ * two ping-ponging query tiles (attention2.cu; correct, measured slower, opt-in with Q3A_ATTN_V2=1), 0 = the encoder's
+ * choice (generation 1 unless that switch is set). */
 int q3a_test_attention_v(const void* qkv_dev, void* out_dev, int T, int H, const int* cu_seqlens, int n_seg,
                          int operand_dtype, int version, void* stream);
 

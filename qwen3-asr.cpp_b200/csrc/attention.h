@@ -32,7 +32,7 @@ int attention2_launch(const void* qkv, void* out, int T, int n_heads, const Attn
 // ---- the aligner decoder's attention (attention_dec.cu): causal, grouped-query, head_dim 128 --------------------------
 // qkv: [n][(H + 2 Hkv) * 128] 16-bit (q | k | v column blocks); out: [n][H * 128] 16-bit
 int attention_dec_launch(const void* qkv, void* out, int n_tokens, int n_heads, int n_kv_heads, int fmt, cudaStream_t stream);
-// which kernel the encoder uses: 2 unless Q3A_ATTN_V1 is set in the environment (A/B runs)
+// which kernel the encoder uses: 1 (kDefaultAttnV2 in common.cuh) unless Q3A_ATTN_V2 is set in the environment (A/B runs)
 int attention_version();
 
 }  // namespace q3a

@@ -49,7 +49,7 @@ def _attn_ref(qkv, H, cu):
     (3, [0, 256, 513, 770, 1027, 1028]), (2, [0, 7805]), (14, [390 * i for i in range(24)])])
 def test_attention_matches_fp32_softmax(lib, opd, tol, H, cu, version):
     """full (one segment per utterance), windowed (104-token segments), ragged and empty segments; both kernel
-    generations (2 = persistent CTAs with two ping-ponging query tiles, what the encoder runs; 1 = one tile per CTA).
+    generations (1 = one tile per CTA, what the encoder runs; 2 = persistent CTAs with two ping-ponging query tiles, opt-in).
     The added shapes hit v2's item boundaries (256 / 257 rows, a one-row tile B), 61 key blocks with many items per
     CTA, and more (item, head) units than SMs so that every CTA walks several items."""
     torch.manual_seed(len(cu) * 100 + H)
