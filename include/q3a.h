@@ -119,6 +119,21 @@ int q3a_mel_batch_device(q3a_frontend* fe, const float* pcm_dev, const int64_t* 
                          int n_clips, float* mel_dev, const int64_t* mel_off, float* max_dev, int finalize,
                          void* stream);
 
+/* Allocation-free variant of q3a_mel_batch_device.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same results (bit-identical); the call performs no cudaMalloc / cudaFree
+ * and no host allocation: its scratch (clip descriptor table and the per-clip maximum slots) is a static __device__
+ * array inside the library (4.5 KB, held by every GPU that loads the library until the process exits), which limits a
+ * call to q3a_mel_noalloc_max_clips() = 128 clips; more is rejected with Q3A_ERR_ARG and a message.  All calls on a
+ * device share that array and it keeps the last call's contents (each call rewrites the table and clears the maxima
+ * itself): calls in one stream are ordered and safe, calls that overlap on one GPU (two streams, two host threads)
+ * race.  The first call on a device resolves the array's device address (cudaGetSymbolAddress; not an allocation, but
+ * not capturable either: make one call before starting a capture). */
+int q3a_mel_batch_device_noalloc(q3a_frontend* fe, const float* pcm_dev, const int64_t* pcm_off, const int* n_samples,
+                                 int n_clips, float* mel_dev, const int64_t* mel_off, float* max_dev, int finalize,
+                                 void* stream);
+int q3a_mel_noalloc_max_clips(void);
+
 /* ---- audio encoder --------------------------------------------------------------------- */
 
 /* replaces AudioEncoder::load_model (audio_encoder.h:25, audio_encoder.cpp:42-83) and the aligner's

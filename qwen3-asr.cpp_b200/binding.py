@@ -51,6 +51,8 @@ SYMBOLS = {
     "q3a_frontend_free": (None, [_P]),
     "q3a_mel_batch": (_I, [_P, _P, _P, _I, _P, _P]),
     "q3a_mel_batch_device": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _I, _P]),
+    "q3a_mel_batch_device_noalloc": (_I, [_P, _P, _P, _P, _I, _P, _P, _P, _I, _P]),
+    "q3a_mel_noalloc_max_clips": (_I, []),
     "q3a_encoder_load": (_I, [C.c_char_p, _I, _I, C.POINTER(_P)]),
     "q3a_encoder_free": (None, [_P]),
     "q3a_encoder_get_hparams": (_I, [_P, C.POINTER(HParams)]),

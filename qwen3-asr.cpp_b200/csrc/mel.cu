@@ -21,6 +21,8 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <mutex>
+#include <string>
 #include <vector>
 
 namespace q3a {
@@ -507,5 +509,126 @@ extern "C" int q3a_mel_batch(q3a_frontend* fe, const float* const* pcm, const in
                                      cudaMemcpyDeviceToHost, st));
     }
     Q3A_CUDA(cudaStreamSynchronize(st));
+    return Q3A_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of q3a_mel_batch_device (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that
+// forbid it).
+//
+// mel_launch keeps two pieces of scratch in grow-only device buffers: the clip descriptor table and the per-clip maximum
+// slots that mel_frames_kernel's atomicMax needs zeroed.  Here both live in one file-scope __device__ array of a fixed
+// size, so the call allocates nothing -- no cudaMalloc / cudaFree, no pinned ring, no host heap either: the clip table
+// travels as a kernel argument (3 KB) to a set-up kernel that writes the descriptors and clears the maxima in place.
+// Every GPU that loads the library holds the array (4.5 KB) until the process exits, every call on a device shares it and
+// it keeps the last call's contents, so two calls that overlap on one GPU (different streams, or two host threads)
+// race; calls in one stream are ordered and safe.
+// ---------------------------------------------------------------------------------------------
+namespace q3a {
+
+constexpr int kNoAllocMaxClips = 128;                    // the stated limit of the entry point
+struct MelNoAllocScratch {
+    MelClipDesc desc[kNoAllocMaxClips];                  // 128 x 32 B
+    unsigned clip_max[kNoAllocMaxClips];                 // 128 x 4 B, cleared by every call
+};
+static __device__ __align__(256) unsigned char g_mel_noalloc_scratch[sizeof(MelNoAllocScratch)];
+
+struct MelNoAllocClips {                                 // by-value kernel argument: 128 x 24 B = 3 KB
+    long long pcm_off[kNoAllocMaxClips];
+    long long mel_off[kNoAllocMaxClips];
+    int n_samples[kNoAllocMaxClips];
+    int tile0[kNoAllocMaxClips];
+};
+
+// device code names the array directly; only the host needs cudaGetSymbolAddress
+__global__ void mel_noalloc_setup_kernel(const __grid_constant__ MelNoAllocClips c, int n_clips) {
+    MelNoAllocScratch& sc = *reinterpret_cast<MelNoAllocScratch*>(g_mel_noalloc_scratch);
+    const int i = threadIdx.x;
+    if (i >= kNoAllocMaxClips) return;
+    if (i < n_clips) {
+        MelClipDesc d;
+        d.pcm_off = c.pcm_off[i]; d.mel_off = c.mel_off[i];
+        d.n_samples = c.n_samples[i]; d.n_len = c.n_samples[i] / kHop;
+        d.tile0 = c.tile0[i]; d.pad = 0;
+        sc.desc[i] = d;
+    }
+    sc.clip_max[i] = 0u;                                 // what must start at zero: the atomicMax slots (all of them)
+}
+
+// The array's name in host code is a host-side stand-in, not a device address: resolve it once per device, with that
+// device current, and hand the kernels the resolved pointer.
+static int mel_noalloc_scratch(int device, MelNoAllocScratch** out) {
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static MelNoAllocScratch* ptr[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) { set_error("mel_batch_device_noalloc: device index out of range"); return Q3A_ERR_ARG; }
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptr[device]) {
+        void* p = nullptr;
+        Q3A_CUDA(cudaGetSymbolAddress(&p, g_mel_noalloc_scratch));    // the caller made `device` current
+        if (!p) { set_error("mel_batch_device_noalloc: cudaGetSymbolAddress returned null"); return Q3A_ERR_CUDA; }
+        ptr[device] = static_cast<MelNoAllocScratch*>(p);
+    }
+    *out = ptr[device];
+    return Q3A_OK;
+}
+
+}  // namespace q3a
+
+extern "C" int q3a_mel_noalloc_max_clips(void) { return kNoAllocMaxClips; }
+
+extern "C" int q3a_mel_batch_device_noalloc(q3a_frontend* fe, const float* pcm_dev, const int64_t* pcm_off,
+                                            const int* n_samples, int n_clips, float* mel_dev, const int64_t* mel_off,
+                                            float* max_dev, int finalize, void* stream) {
+    if (!fe) { set_error("mel_batch_device_noalloc: frontend is null"); return Q3A_ERR_STATE; }
+    if (n_clips < 0 || (n_clips > 0 && (!pcm_dev || !pcm_off || !n_samples || !mel_dev || !mel_off))) {
+        set_error("mel_batch_device_noalloc: null argument"); return Q3A_ERR_ARG;
+    }
+    if (n_clips > kNoAllocMaxClips) {
+        set_error("mel_batch_device_noalloc: n_clips = " + std::to_string(n_clips) + " exceeds the static scratch's maximum of " +
+                  std::to_string(kNoAllocMaxClips) + " clips per call (use q3a_mel_batch_device, or split the batch)");
+        return Q3A_ERR_ARG;
+    }
+    if (n_clips == 0) return Q3A_OK;
+    Q3A_TRY(use_device(fe->device));
+    g_launch_counter = 0;
+    MelNoAllocClips c;                                   // on the stack: no host allocation either
+    int tiles = 0, max_len = 0;
+    for (int b = 0; b < n_clips; ++b) {
+        if (n_samples[b] < 0 || (pcm_off[b] & 3)) { set_error("mel: negative n_samples or pcm offset not a multiple of 4"); return Q3A_ERR_ARG; }
+        const int n_len = n_samples[b] / kHop;
+        c.pcm_off[b] = pcm_off[b]; c.mel_off[b] = mel_off[b]; c.n_samples[b] = n_samples[b]; c.tile0[b] = tiles;
+        tiles += ceil_div(n_len, kFT);
+        if (n_len > max_len) max_len = n_len;
+    }
+    for (int b = n_clips; b < kNoAllocMaxClips; ++b) { c.pcm_off[b] = 0; c.mel_off[b] = 0; c.n_samples[b] = 0; c.tile0[b] = tiles; }
+    MelNoAllocScratch* sc = nullptr;
+    Q3A_TRY(mel_noalloc_scratch(fe->device, &sc));
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    mel_noalloc_setup_kernel<<<1, kNoAllocMaxClips, 0, st>>>(c, n_clips);
+    ++g_launch_counter;
+    Q3A_CUDA(cudaGetLastError());
+    if (tiles > 0) {
+        const int grid = tiles < 2 * fe->n_sms ? tiles : 2 * fe->n_sms;
+        Q3A_CUDA(launch_pdl(mel_frames_kernel, dim3(grid), dim3(kMelThreads), sizeof(MelSmem), st,
+                            pcm_dev, (const MelClipDesc*)sc->desc, n_clips, tiles, (const float*)fe->d_hann,
+                            (const float2*)fe->d_twiddle, (const int*)fe->d_row_bin0, (const int*)fe->d_row_ptr,
+                            (const float*)fe->d_weights, fe->n_mel, mel_dev, (unsigned*)sc->clip_max));
+        ++g_launch_counter;
+        Q3A_CUDA(cudaGetLastError());
+    }
+    if (max_dev) {
+        mel_max_decode_kernel<<<ceil_div(n_clips, 128), 128, 0, st>>>(sc->clip_max, max_dev, n_clips);
+        ++g_launch_counter;
+        Q3A_CUDA(cudaGetLastError());
+    }
+    if (finalize && tiles > 0) {
+        int bpc = ceil_div(ceil_div(fe->n_mel * max_len, 4), 256 * 8);
+        if (bpc < 1) bpc = 1;
+        mel_finalize_kernel<<<n_clips * bpc, 256, 0, st>>>(mel_dev, sc->desc, sc->clip_max, fe->n_mel, bpc);
+        ++g_launch_counter;
+        Q3A_CUDA(cudaGetLastError());
+    }
     return Q3A_OK;
 }
