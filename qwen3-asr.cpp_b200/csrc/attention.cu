@@ -215,15 +215,20 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
             }
             const float neg_m = -m_ref;
             if (n_valid == kKT) {
-                float ps1 = 0.0f;
+                // two keys per FFMA2 / FADD2 (same roundings as the scalar form: results are bit-identical)
+                const uint64_t sc2 = tc::f32x2(kScale, kScale), nm2 = tc::f32x2(neg_m, neg_m);
+                uint64_t ps2 = tc::f32x2(0.0f, 0.0f);
 #pragma unroll
                 for (int i = 0; i < kKT; i += 2) {
-                    const float p0 = tc::ex2_approx(fmaf(__uint_as_float(s[i]), kScale, neg_m));
-                    const float p1 = tc::ex2_approx(fmaf(__uint_as_float(s[i + 1]), kScale, neg_m));
-                    psum += p0; ps1 += p1;
+                    float x0, x1;
+                    tc::f32x2_split(tc::fma_f32x2(tc::f32x2(__uint_as_float(s[i]), __uint_as_float(s[i + 1])), sc2, nm2), x0, x1);
+                    const float p0 = tc::ex2_approx(x0), p1 = tc::ex2_approx(x1);
+                    ps2 = tc::add_f32x2(ps2, tc::f32x2(p0, p1));
                     pk[i >> 1] = OpTraits<OpT>::pack2(p0, p1);
                 }
-                psum += ps1;
+                float ps0, ps1;
+                tc::f32x2_split(ps2, ps0, ps1);
+                psum += ps0; psum += ps1;
             } else {
 #pragma unroll
                 for (int i = 0; i < kKT; i += 16) {
@@ -287,6 +292,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
     // whole 128-byte rows instead of 32 row fragments.
     if (row_live) {
         const float inv = 1.0f / l_run;
+        const uint64_t inv2 = tc::f32x2(inv, inv);
         uint32_t r[64];
         tc::tmem_ld_32x32b_x32(t_row + kKT, *reinterpret_cast<uint32_t(*)[32]>(&r[0]));
         tc::tmem_ld_32x32b_x32(t_row + kKT + 32, *reinterpret_cast<uint32_t(*)[32]>(&r[32]));
@@ -295,10 +301,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const __grid_cons
 #pragma unroll
         for (int g = 0; g < 8; ++g) {
             uint4 u;
-            u.x = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 0]) * inv, __uint_as_float(r[g * 8 + 1]) * inv);
-            u.y = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 2]) * inv, __uint_as_float(r[g * 8 + 3]) * inv);
-            u.z = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 4]) * inv, __uint_as_float(r[g * 8 + 5]) * inv);
-            u.w = OpTraits<OpT>::pack2(__uint_as_float(r[g * 8 + 6]) * inv, __uint_as_float(r[g * 8 + 7]) * inv);
+            float a[8];
+#pragma unroll
+            for (int e = 0; e < 8; e += 2)
+                tc::f32x2_split(tc::mul_f32x2(tc::f32x2(__uint_as_float(r[g * 8 + e]), __uint_as_float(r[g * 8 + e + 1])), inv2), a[e], a[e + 1]);
+            u.x = OpTraits<OpT>::pack2(a[0], a[1]);
+            u.y = OpTraits<OpT>::pack2(a[2], a[3]);
+            u.z = OpTraits<OpT>::pack2(a[4], a[5]);
+            u.w = OpTraits<OpT>::pack2(a[6], a[7]);
             *reinterpret_cast<uint4*>(stage + ((g ^ (tid & 7)) << 4)) = u;
         }
         __syncwarp();
