@@ -30,7 +30,10 @@ RAW_METRICS = [
     "sm__warps_active.avg.pct_of_peak_sustained_active",
     "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
     "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
+    "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__warps_active.avg.per_cycle_active",
+    "smsp__warps_eligible.avg.per_cycle_active", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
 ]
+STALL_RE = re.compile(r"^smsp__average_warps?_(?:latency_)?issue_stalled_(.+?)(?:_per_issue_active)?\.(?:ratio|pct)$")
 
 
 def short_name(full: str) -> str:
@@ -130,10 +133,20 @@ def full_reports(tag: str) -> None:
             for m in RAW_METRICS:
                 if m in col:
                     d[m] = row[col[m]]
+            # the three largest warp-stall reasons (cycles a warp waits per instruction it issues)
+            stalls = []
+            for h, i in col.items():
+                mm = STALL_RE.match(h)
+                if mm and "not_issued" not in h:
+                    try:
+                        stalls.append((float(row[i].replace(",", "")), mm.group(1)))
+                    except ValueError:
+                        pass
+            d["top_stalls"] = "; ".join(f"{n} {v:.2f}" for v, n in sorted(stalls, reverse=True)[:3])
             out_rows.append(d)
     if not out_rows:
         return
-    keys = ["report", "kernel"] + RAW_METRICS
+    keys = ["report", "kernel"] + RAW_METRICS + ["top_stalls"]
     with open(os.path.join(PROF, f"{tag}_kernels.csv"), "w", newline="") as f:
         w = csv.DictWriter(f, fieldnames=keys)
         w.writeheader()
