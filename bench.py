@@ -520,10 +520,22 @@ def run_ours(args):
     # PCM from pinned host memory and downloads its features inside the timed region
     run_e2e_pipelined(2)
     barrier()
+    host_cpu = None
+    try:                                              # whole-box CPU utilisation over the timed e2e region (all ranks' processes)
+        import psutil
+        psutil.cpu_percent(interval=None)
+    except Exception:
+        psutil = None
     t0 = time.perf_counter()
     run_e2e_pipelined(args.steps)
     torch.cuda.synchronize()
     dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+    if psutil is not None:
+        try:
+            host_cpu = {"pct_of_all_cores": psutil.cpu_percent(interval=None), "cores": psutil.cpu_count(),
+                        "what": "box-wide CPU utilisation between the start and the end of this rank's timed e2e region"}
+        except Exception:
+            host_cpu = None
     if world > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     e2e_value = audio_s / float(dt.item())
@@ -661,7 +673,7 @@ def run_ours(args):
                 "with_intra_call_parts_value": e2e_parts_value,
                 "synchronous_call_value": e2e_sync_value,
                 "synchronous_api": "q3a_encode_pcm_batch, one call at a time",
-                "host_link": link},
+                "host_link": link, "host_cpu": host_cpu},
         "gpu_launches": launches0,
         "ranks_share_gpus": emulated,
         "value_checked": value_checked, "value_check": {"against": "q3a_encode_pcm_batch on the same 64 clips (host result)",
