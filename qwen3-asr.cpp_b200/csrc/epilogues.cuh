@@ -25,6 +25,11 @@ __device__ __forceinline__ void store8_f32(float* p, const float (&v)[8]) {
     *(reinterpret_cast<float4*>(p) + 1) = make_float4(v[4], v[5], v[6], v[7]);
 }
 
+// one per-column constant per lane (gemm_tc.cuh EpiCols): lane j of the warp holds column n0 + j's value
+struct Cols1 { float a; };
+struct Cols2 { float a, b; };
+__device__ __forceinline__ float col_of(float lane_value, int j) { return __shfl_sync(0xffffffffu, lane_value, j); }
+
 // ---- staged epilogues (Linear layers): the kernel stores v through smem + TMA ---------------------
 // out[m][n] = act(acc + bias[n])  -> 16-bit operand for the next GEMM
 template <class OpT, bool kGelu>
@@ -32,16 +37,18 @@ struct EpiBiasActOp {
     static constexpr bool kStaged = true, kResidual = false;
     static constexpr int kOutBytes = 2;
     const float* bias;
+    using Cols = Cols1;
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
-    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
+    __device__ __forceinline__ Cols cols(int n0, int nvalid, int lane) const {
+        return Cols{bias && lane < nvalid ? __ldg(bias + n0 + lane) : 0.0f};
+    }
+    __device__ __forceinline__ void apply(int, int, int nvalid, float (&v)[32], const Cols& cv) const {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float b[8];
-                if (bias) load8(bias + n0 + g * 8, b);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    float x = v[g * 8 + j] + (bias ? b[j] : 0.0f);
+                    float x = v[g * 8 + j] + col_of(cv.a, g * 8 + j);
                     v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
                 }
             }
@@ -56,15 +63,17 @@ struct EpiBiasF32 {
     static constexpr int kOutBytes = 4;
     const float* bias;
     int prefetch = 1;        // residual epilogues: L2-prefetch the next tile's residual rows (gemm_tc.cuh)
-    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
+    using Cols = Cols1;
+    __device__ __forceinline__ Cols cols(int n0, int nvalid, int lane) const {
+        return Cols{bias && lane < nvalid ? __ldg(bias + n0 + lane) : 0.0f};
+    }
+    __device__ __forceinline__ void apply(int, int, int nvalid, float (&v)[32], const Cols& cv) const {
         if (!bias) return;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float b[8];
-                load8(bias + n0 + g * 8, b);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[g * 8 + j] += b[j];
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] += col_of(cv.a, g * 8 + j);
             }
         }
     }
@@ -108,15 +117,17 @@ struct EpiBiasF32Dual {
     float2* stats; int n_part;
     int prefetch = 1;
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
-    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32]) const {
+    using Cols = Cols1;
+    __device__ __forceinline__ Cols cols(int n0, int nvalid, int lane) const {
+        return Cols{bias && lane < nvalid ? __ldg(bias + n0 + lane) : 0.0f};
+    }
+    __device__ __forceinline__ void apply(int, int, int nvalid, float (&v)[32], const Cols& cv) const {
         if (!bias) return;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float b[8];
-                load8(bias + n0 + g * 8, b);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) v[g * 8 + j] += b[j];
+                for (int j = 0; j < 8; ++j) v[g * 8 + j] += col_of(cv.a, g * 8 + j);
             }
         }
     }
@@ -170,16 +181,17 @@ struct EpiLnFoldActOp {
     int rms;                 // 1: RMSNorm (no mean subtraction; the aligner's decoder, forced_aligner.cpp:1012-1013)
     __device__ __forceinline__ static uint32_t pack2(float a, float b) { return OpTraits<OpT>::pack2(a, b); }
     __device__ __forceinline__ RowState row_state(int m) const { return ln_row_state(stats, n_part, M, inv_d, eps, rms, m); }
-    __device__ __forceinline__ void apply(int, int n0, int nvalid, float (&v)[32], const RowState& rs) const {
+    using Cols = Cols2;      // a = c[n], b = s[n]
+    __device__ __forceinline__ Cols cols(int n0, int nvalid, int lane) const {
+        return lane < nvalid ? Cols{__ldg(c + n0 + lane), __ldg(s + n0 + lane)} : Cols{0.0f, 0.0f};
+    }
+    __device__ __forceinline__ void apply(int, int, int nvalid, float (&v)[32], const RowState& rs, const Cols& cv) const {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
             if (g * 8 < nvalid) {
-                float cc[8], ss[8];
-                load8(c + n0 + g * 8, cc);
-                load8(s + n0 + g * 8, ss);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    const float x = fmaf(rs.rstd, fmaf(-rs.mean, ss[j], v[g * 8 + j]), cc[j]);
+                    const float x = fmaf(rs.rstd, fmaf(-rs.mean, col_of(cv.b, g * 8 + j), v[g * 8 + j]), col_of(cv.a, g * 8 + j));
                     v[g * 8 + j] = kGelu ? gelu_tanh(x) : x;
                 }
             }

@@ -67,6 +67,12 @@ using GemmSmemFor = GemmSmem<BLOCK_N, Epi::kStaged ? 32 * 32 * Epi::kOutBytes + 
 struct NoRowState {};
 template <class Epi, class = void> struct EpiRowState { using type = NoRowState; };
 template <class Epi> struct EpiRowState<Epi, decltype((void)sizeof(typename Epi::RowState))> { using type = typename Epi::RowState; };
+// per-column constants of a 32-column chunk (bias, fold constants), one column per lane: requested before the accumulator
+// load so that their latency runs under it, read back by column with a shuffle.  (Every thread loading all 32 values itself
+// exposed four dependent L2 round trips per chunk: 13 % of the stall samples of the FFN-up GEMM, profiles/r2n.)
+struct NoCols {};
+template <class Epi, class = void> struct EpiCols { using type = NoCols; };
+template <class Epi> struct EpiCols<Epi, decltype((void)sizeof(typename Epi::Cols))> { using type = typename Epi::Cols; };
 
 // ---- A-operand coordinate policies (m128 = index of this CTA's 128-row block) -----------------
 // The producer and the MMA issuer walk the K blocks of a tile with a small iterator that is advanced
@@ -430,17 +436,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // chunk's store is still reading, so it goes out after the accumulator load and the functor, by which
                 // time that read has long finished and lane 0 does not hold up the warp's aligned tcgen05.ld.
                 if constexpr (kEpiBufs > 2) prefetch_next_residual();
+                typename EpiCols<Epilogue>::type cv{};
+                constexpr bool kHasCols = !std::is_same<typename EpiCols<Epilogue>::type, NoCols>::value;
+                if constexpr (kHasCols) cv = epi.cols(n0, nvalid, lane);
                 uint32_t r[32];
                 tc::tmem_ld_32x32b_x32(t_row + c * 32, r);
                 tc::tmem_ld_wait();
+                if (c + kEpiPerQuad >= nch) {
+                    // this warp's last tcgen05.ld of the tile has completed: hand its share of the accumulator buffer back
+                    // to the MMA issuer now, before the arithmetic and the stores of the chunk
+                    tc::fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive_peer_tmem(as ? tempty_leader1 : tempty_leader0);
+                }
                 float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
                 if constexpr (!kStaged) {
                     if (m < M) epi(m, n0, nvalid, v);
                 } else {
-                    if constexpr (std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value) epi.apply(m, n0, nvalid, v);
-                    else epi.apply(m, n0, nvalid, v, rs);
+                    constexpr bool kHasRS = !std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value;
+                    if constexpr (kHasRS && kHasCols) epi.apply(m, n0, nvalid, v, rs, cv);
+                    else if constexpr (kHasRS) epi.apply(m, n0, nvalid, v, rs);
+                    else if constexpr (kHasCols) epi.apply(m, n0, nvalid, v, cv);
+                    else epi.apply(m, n0, nvalid, v);
                     if constexpr (kEpiBufs <= 2) prefetch_next_residual();
                     const int b = seq % kEpiBufs;
                     uint8_t* buf = my_bufs_gen + b * kBufBytes;
@@ -507,10 +526,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                 // warp owned no chunk of the tile) so that the consumer can add all of them in a fixed order
                 if (m < M) epi.stats[(size_t)m * epi.n_part + n_blk * 2 + hf] = make_float2(st_sum, st_sq);
             }
-            // every tcgen05.ld of this tile has completed: hand the accumulator buffer back to the MMA issuer
-            tc::fence_before_sync();
-            __syncwarp();
-            if (lane == 0) tc::mbar_arrive_cluster(as ? tempty_leader1 : tempty_leader0);
+            if (hf >= nch) {                               // a warp that owned no chunk of this tile still owes its arrival
+                tc::fence_before_sync();
+                __syncwarp();
+                if (lane == 0) tc::mbar_arrive_peer_tmem(as ? tempty_leader1 : tempty_leader0);
+            }
         }
         if (kStaged && lane == 0) tc::bulk_wait_group<0>();
     }

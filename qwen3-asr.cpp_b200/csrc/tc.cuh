@@ -201,6 +201,13 @@ __device__ __forceinline__ uint32_t mapa(uint32_t saddr, uint32_t rank) {
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
+// Arrive on a peer CTA's barrier for a hand-off whose payload is TMEM, not memory: the reads are complete (tcgen05.wait::ld)
+// and ordered by tcgen05.fence::before_thread_sync, so the default release at CTA scope is enough.  The cluster-scope
+// release above compiles to MEMBAR.ALL.GPU, which waits for every store the thread has in flight: measured at 15-20 % of the
+// epilogue warps' time in the 12-warp GEMMs (profiles/r2n, source view).
+__device__ __forceinline__ void mbar_arrive_peer_tmem(uint32_t cluster_addr) {
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
 // TMA loads whose completion bytes are signalled on an mbarrier of either CTA of the pair
 __device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const void* tmap, uint32_t bar_cluster, int c0, int c1) {
     asm volatile(
