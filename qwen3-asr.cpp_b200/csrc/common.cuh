@@ -194,6 +194,9 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 constexpr bool kDefaultAttnV2 = false;       // attention2.cu instead of attention.cu          Q3A_ATTN_V2 / Q3A_ATTN_V1
                                              // (validated r2a: all 76 parity cases green, but 157 us against 133 us per
                                              //  layer on the bench shape -- DESIGN.md 4.4 -- so the first kernel stays default)
+constexpr int kDefaultDualEpiWarps = 4;      // epilogue warps of the residual GEMMs with a 16-bit copy   Q3A_DUAL_EPI_WARPS=4|8
+                                             // (validated r2s: bit-identical, FFN-down 149.7 -> 134.6 us: a fifth ring stage)
+constexpr int kDefaultResEpiWarps = 8;       // the same for the plain residual GEMM                      Q3A_RES_EPI_WARPS=4|8
 constexpr bool kDefaultLnFold = true;        // LayerNorm folded into the GEMMs                Q3A_LN_FOLD / Q3A_NO_LN_FOLD
 constexpr bool kDefaultQ8Fused = false;      // Q8_0 weights dequantised inside the GEMM       Q3A_Q8_FUSED / Q3A_Q8_DEQUANT_AT_LOAD
                                              // (validated bit-identical, halves the weight arena, but 36.0 against 22.3 ms per

@@ -87,6 +87,17 @@ static int launch_linear(const LinearArgs& a, const Epi& epi, cudaStream_t strea
     if constexpr (Epi::kStaged && Epi::kOutBytes == 2) {
         if (epi_warps_16bit() == 12) return launch_linear_ew<BLOCK_N, kFmt, Epi, 12>(a, epi, stream);
     }
+    if constexpr (EpiDual<Epi>::value && Epi::kResidual) {
+        // FFN-down / out-projection with the 16-bit copy: K is long, the epilogue has time; four warps halve the staging
+        // and buy a fifth ring stage for the operand stream the MMAs were waiting for (Q3A_DUAL_EPI_WARPS=4|8)
+        const char* e = getenv("Q3A_DUAL_EPI_WARPS");        // read per launch: the parity test switches it
+        if ((e ? atoi(e) : kDefaultDualEpiWarps) == 4) return launch_linear_ew<BLOCK_N, kFmt, Epi, 4>(a, epi, stream);
+    }
+    if constexpr (!EpiDual<Epi>::value && Epi::kResidual) {
+        // the plain residual GEMM (out-projection at fold mask 5): same trade, its own switch (Q3A_RES_EPI_WARPS=4|8)
+        const char* e = getenv("Q3A_RES_EPI_WARPS");
+        if ((e ? atoi(e) : kDefaultResEpiWarps) == 4) return launch_linear_ew<BLOCK_N, kFmt, Epi, 4>(a, epi, stream);
+    }
     return launch_linear_ew<BLOCK_N, kFmt, Epi, 8>(a, epi, stream);
 }
 

@@ -177,8 +177,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
     using S = GemmSmemFor<BLOCK_N, Epilogue, kWq8, kEW>;
     constexpr int kStages = S::kStages;
     constexpr int kEpiPerQuad = kEW / 4;                                // epilogue warps sharing a TMEM lane quadrant
-    static_assert(kEW == 8 || kEW == 12, "8 or 12 epilogue warps");
-    static_assert(!EpiDual<Epilogue>::value || kEW == 8, "the dual-output statistics layout assumes two warps per quadrant");
+    static_assert(kEW == 4 || kEW == 8 || kEW == 12, "4, 8 or 12 epilogue warps");
+    static_assert(!EpiDual<Epilogue>::value || kEW <= 8, "the dual-output statistics layout has two partials per column block");
     static_assert(BLOCK_N % 16 == 0 && BLOCK_N <= 256, "BLOCK_N must be a multiple of 16, at most 256");
     static_assert(!kStaged || BLOCK_N % 32 == 0, "staged epilogues store whole 32-column chunks");
     static_assert(!kResidual || kOutBytes == 4, "the residual stream is fp32");
@@ -416,7 +416,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             const uint32_t t_row = tmem_base + as * 256 + ((uint32_t)(q * 32) << 16);
             typename EpiRowState<Epilogue>::type rs{};
             if constexpr (!std::is_same<typename EpiRowState<Epilogue>::type, NoRowState>::value) rs = epi.row_state(m);
-            float st_sum = 0.0f, st_sq = 0.0f;             // dual output: this warp's share of the row's statistics
+            // dual output: this warp's share of the row's statistics.  The two partials of a column block are the sums over
+            // its even and its odd 32-column chunks -- with eight warps that is one warp each, with four the one warp keeps
+            // both, so the statistics (and everything downstream) are bit-identical for either count.
+            float st_sum = 0.0f, st_sq = 0.0f, st_sum1 = 0.0f, st_sq1 = 0.0f;
 #pragma unroll 1
             for (int c = hf; c < nch; c += kEpiPerQuad) {
                 const int n0 = n_blk * BLOCK_N + c * 32;
@@ -501,7 +504,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
                         for (int j = 0; j < 4; ++j) {
                             if (j * 8 < nvalid) {
 #pragma unroll
-                                for (int i = 0; i < 8; ++i) { st_sum += v[8 * j + i]; st_sq = fmaf(v[8 * j + i], v[8 * j + i], st_sq); }
+                                for (int i = 0; i < 8; ++i) {
+                                    if (kEW == 4 && (c & 1)) { st_sum1 += v[8 * j + i]; st_sq1 = fmaf(v[8 * j + i], v[8 * j + i], st_sq1); }
+                                    else { st_sum += v[8 * j + i]; st_sq = fmaf(v[8 * j + i], v[8 * j + i], st_sq); }
+                                }
                             }
                             uint4 u;
                             u.x = Epilogue::pack2(v[8 * j + 0], v[8 * j + 1]);
@@ -524,7 +530,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant
             if constexpr (kDual) {
                 // one (sum, sum of squares) partial per (row, column block, warp half), always written (zeros when this
                 // warp owned no chunk of the tile) so that the consumer can add all of them in a fixed order
-                if (m < M) epi.stats[(size_t)m * epi.n_part + n_blk * 2 + hf] = make_float2(st_sum, st_sq);
+                if (m < M) {
+                    epi.stats[(size_t)m * epi.n_part + n_blk * 2 + hf] = make_float2(st_sum, st_sq);
+                    if constexpr (kEW == 4) epi.stats[(size_t)m * epi.n_part + n_blk * 2 + 1] = make_float2(st_sum1, st_sq1);
+                }
             }
             if (hf >= nch) {                               // a warp that owned no chunk of this tile still owes its arrival
                 tc::fence_before_sync();

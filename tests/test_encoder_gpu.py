@@ -611,3 +611,20 @@ def test_conv_k_order_only_changes_the_summation_order(lib, asr_model, filters, 
         assert cos >= COS and rel <= REL, (env, cos, rel)
     cos, rel = compare(outs[0], outs[1])
     assert cos >= 0.999999 and rel <= 1e-3, (cos, rel)
+
+
+@pytest.mark.parametrize("opd", [B.OP_BF16, B.OP_F16])
+def test_residual_gemm_epilogue_warp_count_does_not_change_a_bit(lib, asr_model, filters, monkeypatch, opd):
+    """The residual GEMMs that also emit the 16-bit copy and the LayerNorm partials run four or eight epilogue warps
+    (Q3A_DUAL_EPI_WARPS; four leave room for a fifth operand ring stage).  The partials keep their layout -- sums over the
+    even and over the odd 32-column chunks of a column block -- so the features are bit-identical for either count."""
+    shape, paths, Ws = asr_model
+    mels = [MO.log_mel_numpy(synth.synth_audio(311 + i, n), filters) for i, n in enumerate((16000 * 6 + 77, 16000 * 31 + 5, 4000))]
+    outs = []
+    for ew in ("8", "4"):
+        monkeypatch.setenv("Q3A_DUAL_EPI_WARPS", ew)
+        enc = B.Encoder(paths["f16"], 0, opd)
+        outs.append(enc.encode_batch(mels, B.MODE_ASR))
+        enc.close()
+    for a, b in zip(*outs):
+        assert np.isfinite(a).all() and np.array_equal(a, b)
