@@ -75,3 +75,29 @@ def test_fma_pipe_exp2_accuracy():
     y = (p.view(np.uint32) + (t.view(np.uint32) << np.uint32(23))).astype(np.uint32).view(f)
     ref = np.exp2(xc.astype(np.float64))
     assert np.abs(r).max() <= 0.5 and (np.abs(y - ref) / ref).max() <= 5e-6
+
+
+def test_gemm_shared_memory_plan_and_epilogue_statistics_layout():
+    """Restates gemm_tc.cuh's GemmSmem arithmetic: the ring depth every Linear GEMM of the encoder gets for its epilogue
+    warp count, and that the statistics partials of a column block (sums over its even / odd 32-column chunks) are the same
+    sets of chunks whether one warp (kEW = 4) or two (kEW = 8) own a TMEM lane quadrant."""
+    limit, barrier = 232448, 512
+
+    def stages(block_n, out_bytes, dual, residual, kew, staged=True):
+        a, b = 128 * 64 * 2, (block_n // 2) * 64 * 2
+        buf = (32 * 32 * out_bytes + (32 * 32 * 2 if dual else 0)) if staged else 0
+        bufs = (3 if residual and not dual else 2) if staged else 0
+        avail = limit - 1024 - barrier - kew * bufs * buf
+        assert (a + b) % 1024 == 0
+        return min(6, avail // (a + b))
+
+    assert stages(240, 2, False, False, 8, staged=False) == 6        # conv2 / conv3
+    assert stages(224, 2, False, False, 12) == 5                      # QKV with attn_norm folded in
+    assert stages(256, 2, False, False, 12) == 5                      # FFN-up + GELU
+    assert stages(224, 4, False, True, 8) == 4                        # out-projection + residual
+    assert stages(224, 4, True, True, 8) == 4                         # FFN-down, eight epilogue warps
+    assert stages(224, 4, True, True, 4) == 5                         # ... four: the fifth stage (DESIGN.md 4.1)
+    for nch in range(1, 9):                                           # chunks of a column block (7 for BLOCK_N = 224)
+        eight = [[c for c in range(hf, nch, 2)] for hf in (0, 1)]     # warp hf of a quadrant takes c = hf, hf + 2, ...
+        four = [[c for c in range(nch) if c % 2 == p] for p in (0, 1)]
+        assert eight == four
